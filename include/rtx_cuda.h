@@ -1,0 +1,192 @@
+/* rtx_cuda.h — C ABI of the B200-native render hot path for the `rtx` (rust-raytracing) crate.
+ *
+ * This is the drop-in boundary: plain pointers and sizes, no C++/torch types.  Every struct is a
+ * layout-compatible mirror of a reference type (the Rust side declares them #[repr(C)]); every entry
+ * point names the reference interface it replaces (paths relative to the reference's src/).
+ *
+ * The path behind it — camera-ray generation, nearest-hit ray/sphere + ray/plane + ray/triangle,
+ * shade/bounce/accumulate — runs ONLY as hand-written CUDA (sm_100a).  There is no CPU fallback: every
+ * render entry point returns RTX_ERR_CUDA when no usable device exists.
+ *
+ * Numerics contract: all path arithmetic is IEEE-754 binary64, round-to-nearest, NEVER fused
+ * (the reference is Rust f64, which does not contract a*b+c).  Results are a pure function of
+ * (scene, width, height, seed): independent of GPU count, tile shape and launch shape.
+ */
+#ifndef RTX_CUDA_H_
+#define RTX_CUDA_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define RTX_CUDA_ABI_VERSION 1
+
+/* ---- mirrors ------------------------------------------------------------------------------- */
+typedef struct { double x, y, z; } rtx_vec3;                 /* math/vector.rs:12-20           24 B */
+typedef struct { rtx_vec3 x, y, z; } rtx_mat3;               /* math/mat.rs:10-18 (ROW vectors) 72 B */
+typedef struct {                                             /* raytracing/camera.rs:7-15     200 B */
+  double   fov;                                              /*   horizontal, radians               */
+  rtx_vec3 position;
+  rtx_vec3 direction;
+  rtx_mat3 to_cam_space;
+  rtx_mat3 to_world_space;
+} rtx_camera;
+typedef struct {                                             /* raytracing/scene.rs:16-28      40 B */
+  uint64_t rays_per_pixel;                                   /*   usize                             */
+  uint64_t max_bounces;                                      /*   usize; loop runs max_bounces + 1  */
+  double   focal_length;
+  double   focal_offset;
+  double   non_focal_offset;
+} rtx_config;
+typedef struct {                                             /* raytracing/object.rs:79-89     56 B */
+  rtx_vec3 base_color;
+  rtx_vec3 emission_color;
+  double   roughness;
+} rtx_material;
+typedef struct { rtx_vec3 position; double radius; } rtx_sphere;   /* object/sphere.rs:9-12    32 B */
+typedef struct { rtx_vec3 position, normal; } rtx_plane;           /* object/plane.rs:9-12     48 B */
+typedef struct { rtx_vec3 vertices[3]; } rtx_triangle;             /* object/triangle.rs:9-11  72 B */
+
+typedef struct rtx_scene rtx_scene;                          /* opaque; ≙ raytracing/scene.rs:78-85 */
+
+/* ---- status -------------------------------------------------------------------------------- */
+typedef int32_t rtx_status;
+enum {
+  RTX_OK                    = 0,
+  RTX_ERR_INVALID_ARGUMENT  = 1,
+  RTX_ERR_CUDA              = 2,  /* no device / CUDA runtime error (message in rtx_last_error)     */
+  RTX_ERR_OUT_OF_MEMORY     = 3,
+  RTX_ERR_UNSUPPORTED_SHAPE = 4,  /* user-defined CustomShape (object.rs:53-76) cannot cross the ABI */
+  RTX_ERR_INTERNAL          = 5
+};
+
+/* ---- render flags -------------------------------------------------------------------------- */
+enum {
+  RTX_ACCEL_AUTO      = 0u,       /* brute force for small scenes, LBVH above a primitive threshold  */
+  RTX_ACCEL_BRUTE     = 1u,       /* scene.rs:243-251 as written: O(N) scan                          */
+  RTX_ACCEL_LBVH      = 2u,       /* GPU-built Morton LBVH; identical results to RTX_ACCEL_BRUTE     */
+  RTX_ACCEL_MASK      = 3u,
+  RTX_FLAG_NO_RADIANCE = 4u       /* hit-ID-only render (out_rgb may be NULL)                        */
+};
+
+/* Per-render statistics (all ranks report their own shard). */
+typedef struct {
+  uint64_t rays;            /* closest_object queries executed (scene.rs:231) — the metric's "ray"   */
+  uint64_t paths;           /* camera samples started                                                */
+  uint64_t pixels;          /* pixels this call rendered                                             */
+  uint64_t triangle_panics; /* hits rejected where the reference's assert_eq! (triangle.rs:76-94) would abort */
+  float    device_ms;       /* CUDA-event time of the render kernel(s) on the launching stream       */
+  float    total_ms;        /* host-side wall time of the whole call (copies included)               */
+  uint32_t kernel_launches; /* kernels launched by this call                                         */
+  uint32_t accel_used;      /* RTX_ACCEL_BRUTE or RTX_ACCEL_LBVH                                     */
+  uint64_t nodes_visited;   /* LBVH: internal nodes popped (0 for brute force)                       */
+  uint64_t prims_tested;    /* primitive distance evaluations                                        */
+} rtx_stats;
+
+/* Image shard for multi-GPU rendering: the image is cut into RTX_TILE×RTX_TILE pixel tiles numbered
+ * row-major; this call renders tiles t with t % count == index (interleaved for load balance). */
+#define RTX_TILE 16u
+typedef struct { uint32_t index, count; } rtx_shard;
+
+/* ---- host-side helpers (plain f64, same evaluation order as the reference) ---------------------- */
+/* ≙ Camera::new                       raytracing/camera.rs:19-28 (+ derive_to_world_space_mat :42-49) */
+rtx_status rtx_camera_new(const rtx_vec3* position, const rtx_vec3* direction, double fov, rtx_camera* out);
+/* ≙ Camera::set_direction             raytracing/camera.rs:35-40 — matrices lag one call, as upstream */
+rtx_status rtx_camera_set_direction(rtx_camera* camera, const rtx_vec3* direction);
+/* ≙ Camera::to_cam_space / to_world_space / rotate_to_world_space   raytracing/camera.rs:51-67       */
+rtx_status rtx_camera_to_cam_space(const rtx_camera* camera, const rtx_vec3* v, rtx_vec3* out);
+rtx_status rtx_camera_to_world_space(const rtx_camera* camera, const rtx_vec3* v, rtx_vec3* out);
+rtx_status rtx_camera_rotate_to_world_space(const rtx_camera* camera, const rtx_vec3* v, rtx_vec3* out);
+/* ≙ Config::default                   raytracing/scene.rs:55-65                                     */
+rtx_status rtx_config_default(rtx_config* out);
+
+/* ---- scene lifetime ------------------------------------------------------------------------ */
+/* ≙ Scene::new                        raytracing/scene.rs:112-118.  device = CUDA ordinal.          */
+rtx_status rtx_scene_create(const rtx_camera* camera, const rtx_config* config, int32_t device, rtx_scene** out);
+rtx_status rtx_scene_destroy(rtx_scene* scene);
+/* ≙ pub fields Scene.camera / Scene.config   raytracing/scene.rs:80-84                              */
+rtx_status rtx_scene_set_camera(rtx_scene* scene, const rtx_camera* camera);
+rtx_status rtx_scene_set_config(rtx_scene* scene, const rtx_config* config);
+rtx_status rtx_scene_get_camera(const rtx_scene* scene, rtx_camera* out);
+rtx_status rtx_scene_get_config(const rtx_scene* scene, rtx_config* out);
+/* ≙ Scene::add_object ×n              raytracing/scene.rs:126-128.  Object index = global insertion
+ * order across all three calls (it is the nearest-hit tie-break, scene.rs:250).                    */
+rtx_status rtx_scene_add_spheres(rtx_scene* scene, const rtx_sphere* shapes, const rtx_material* materials, uint64_t n);
+rtx_status rtx_scene_add_planes(rtx_scene* scene, const rtx_plane* shapes, const rtx_material* materials, uint64_t n);
+rtx_status rtx_scene_add_triangles(rtx_scene* scene, const rtx_triangle* shapes, const rtx_material* materials, uint64_t n);
+rtx_status rtx_scene_clear_objects(rtx_scene* scene);
+uint64_t   rtx_scene_object_count(const rtx_scene* scene);
+
+/* ---- render -------------------------------------------------------------------------------- */
+/* ≙ Scene::render                     raytracing/scene.rs:144-170.  HOST buffers; blocks until done.
+ * out_rgb: double[height][width][3], row 0 = bottom of the picture, linear unclamped radiance
+ * (≙ Vec<Vec<Vector3>> img[y][x]).  out_primary_hit_id: uint32[height][width] (object index hit by the
+ * first ray of sample 0; 0xFFFFFFFF = miss) or NULL.  seed: selects the RNG streams (the reference
+ * has no seed — its thread-local fastrand is time-seeded).                           */
+rtx_status rtx_scene_render(rtx_scene* scene, uint32_t width, uint32_t height, uint64_t seed, uint32_t flags,
+                            double* out_rgb, uint32_t* out_primary_hit_id, rtx_stats* out_stats);
+
+/* Device-resident variant, asynchronous on `cuda_stream` (a cudaStream_t; NULL = default stream).
+ * Renders the tiles of `shard` (NULL = whole image).  With shard->count == 1 (or NULL) d_out_rgb /
+ * d_out_primary_hit_id use the full-image layout above.  With count > 1 they are COMPACT: local tile
+ * j (global tile j*count + index) occupies [j][RTX_TILE][RTX_TILE][3] doubles / [j][RTX_TILE][RTX_TILE]
+ * ids — equal-sized per-rank buffers that a gather concatenates (see rtx_deinterleave_tiles).
+ * d_out_counters: uint64[3] device counters {rays, paths, triangle_panics} to accumulate into, or
+ * NULL.  Time it with events on your stream.                                                       */
+rtx_status rtx_scene_render_device(rtx_scene* scene, uint32_t width, uint32_t height, uint64_t seed, uint32_t flags,
+                                   const rtx_shard* shard, void* d_out_rgb, void* d_out_primary_hit_id,
+                                   void* d_out_counters, void* cuda_stream);
+/* Number of tiles (and therefore compact-buffer slots) shard `index` of `count` owns. */
+uint64_t   rtx_shard_tile_count(uint32_t width, uint32_t height, uint32_t index, uint32_t count);
+/* Scatter gathered compact shard buffers (rank-major: [count][slots][RTX_TILE][RTX_TILE][...]) into
+ * the full image layout on the device.  ≙ the row-ordered join of scene.rs:167-169.  Either pair of
+ * pointers may be NULL.  slots = rtx_shard_tile_count(width, height, 0, count).                     */
+rtx_status rtx_deinterleave_tiles(uint32_t width, uint32_t height, uint32_t count,
+                                  const void* d_gathered_rgb, void* d_out_rgb,
+                                  const void* d_gathered_ids, void* d_out_ids, void* cuda_stream);
+
+/* ≙ Scene::render_to_image            raytracing/scene.rs:173-178: vertical flip, ×256, saturating
+ * `as u8`, no gamma.  out: uint8[height][width][3] (HOST), row 0 = top of the picture.             */
+rtx_status rtx_scene_render_to_rgb8(rtx_scene* scene, uint32_t width, uint32_t height, uint64_t seed, uint32_t flags,
+                                    uint8_t* out_rgb8, rtx_stats* out_stats);
+/* Device-side quantiser used by the call above (d_rgb: full-image doubles → d_out: uint8 image). */
+rtx_status rtx_quantize_rgb8_device(const void* d_rgb, uint32_t width, uint32_t height, void* d_out_rgb8, void* cuda_stream);
+
+/* ---- diagnostics --------------------------------------------------------------------------- */
+/* Message for the most recent failure on `scene` (or the last scene-less failure when NULL). */
+const char* rtx_last_error(const rtx_scene* scene);
+uint32_t    rtx_abi_version(void);
+/* Number of usable CUDA devices (0 when none: every render call then fails with RTX_ERR_CUDA). */
+int32_t     rtx_device_count(void);
+/* Pinned host memory for out_rgb / out_primary_hit_id (optional; makes the D2H copy a single DMA). */
+rtx_status  rtx_host_alloc(size_t bytes, void** out);
+rtx_status  rtx_host_free(void* p);
+
+/* Measured FP64 issue-rate peaks of the device, the roofline denominators for the brute-force regime
+ * (non-fused DADD+DMUL, as the parity contract forbids FMA; and DFMA for context).  Tflop/s.       */
+rtx_status rtx_probe_fp64_peak(int32_t device, double* out_nonfused_tflops, double* out_fma_tflops);
+
+/* Per-function device evaluation for parity tests (HOST buffers, n items each).
+ * rays[n][6] = position.xyz, direction.xyz.                                                        */
+/* ≙ Scene::closest_object             raytracing/scene.rs:243-251 */
+rtx_status rtx_debug_closest_object(rtx_scene* scene, uint32_t flags, const double* rays, uint64_t n,
+                                    double* out_t, uint32_t* out_id);
+/* ≙ Object::normal_at                 raytracing/object.rs:37-39 — ids[n], positions[n][3] → out[n][3] */
+rtx_status rtx_debug_normal_at(rtx_scene* scene, const uint32_t* ids, const double* positions, uint64_t n, double* out);
+/* ≙ random_bounce_dir                 raytracing/scene.rs:279-291 — in[n][7] = dir.xyz, normal.xyz,
+ * roughness; states[n] = WyRand stream states (updated) → out[n][3]                                */
+rtx_status rtx_debug_random_bounce_dir(int32_t device, uint64_t* states, const double* in, uint64_t n, double* out);
+/* ≙ fastrand::f64()                   call sites math/vector.rs:31-33,37-38 — n draws from *state   */
+rtx_status rtx_debug_wyrand_f64(int32_t device, uint64_t* state, uint64_t n, double* out);
+/* Returns fl(fl(a*b)+c) as the library's device code computes `a*b+c`: proves no FMA contraction.  */
+rtx_status rtx_debug_contraction_probe(int32_t device, double a, double b, double c, double* out);
+/* The seeding convention: WyRand state of the stream with the given key. */
+uint64_t   rtx_stream_state(uint64_t seed, uint64_t key);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* RTX_CUDA_H_ */

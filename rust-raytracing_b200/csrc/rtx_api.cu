@@ -1,0 +1,587 @@
+// rtx_api.cu — the C ABI declared in include/rtx_cuda.h: scene lifetime, upload, render entry points.
+//
+// Host-side mirror of raytracing/scene.rs (Scene::new / add_object / render / render_to_image) and
+// raytracing/camera.rs (Camera::new / set_direction / to_*_space).  The hot path itself lives in
+// rtx_render.cu; nothing here computes a pixel on the CPU.
+#include <chrono>
+#include <cstring>
+
+#include "rtx_internal.h"
+#include "rtx_trace.cuh"
+
+namespace rtx {
+
+static thread_local std::string g_last_error;
+
+rtx_status fail(const rtx_scene* s, rtx_status code, const std::string& msg) {
+  g_last_error = msg;
+  if (s) s->last_error = msg;
+  return code;
+}
+rtx_status cuda_fail(const rtx_scene* s, cudaError_t e, const char* what) {
+  std::string msg = std::string("CUDA error: ") + cudaGetErrorName(e) + " (" + cudaGetErrorString(e) + ") in " + what;
+  cudaGetLastError();  // clear the sticky-less error state
+  return fail(s, e == cudaErrorMemoryAllocation ? RTX_ERR_OUT_OF_MEMORY : RTX_ERR_CUDA, msg);
+}
+
+static inline V3 to_v3(const rtx_vec3& v) { return mk3(v.x, v.y, v.z); }
+static inline rtx_vec3 from_v3(V3 v) {
+  rtx_vec3 r;
+  r.x = v.x, r.y = v.y, r.z = v.z;
+  return r;
+}
+static inline M3 to_m3(const rtx_mat3& m) {
+  M3 r;
+  r.x = to_v3(m.x), r.y = to_v3(m.y), r.z = to_v3(m.z);
+  return r;
+}
+static inline rtx_mat3 from_m3(const M3& m) {
+  rtx_mat3 r;
+  r.x = from_v3(m.x), r.y = from_v3(m.y), r.z = from_v3(m.z);
+  return r;
+}
+
+// raytracing/camera.rs:42-49
+static M3 derive_to_world_space_mat(V3 direction) {
+  const V3 cam_forward = vnorm(direction);
+  const V3 cam_right = cross(cam_forward, mk3(0., 0., -1.));
+  const V3 cam_up = cross(cam_forward, cam_right);
+  M3 m;
+  m.x = cam_right, m.y = cam_up, m.z = cam_forward;
+  return transpose(m);
+}
+
+template <typename T>
+static cudaError_t grow(T** p, size_t* cap, size_t need_bytes) {
+  if (*cap >= need_bytes && *p) return cudaSuccess;
+  if (*p) cudaFree(*p);
+  *p = nullptr;
+  *cap = 0;
+  cudaError_t e = cudaMalloc((void**)p, need_bytes);
+  if (e == cudaSuccess) *cap = need_bytes;
+  return e;
+}
+
+static inline uint32_t align16(size_t v) { return (uint32_t)((v + 15) & ~(size_t)15); }
+
+rtx_status ensure_uploaded(rtx_scene* s, cudaStream_t stream) {
+  if (!s->dirty && s->d_blob) return RTX_OK;
+  SceneLayout L{};
+  L.n_obj = (uint32_t)s->n_obj;
+  L.n_sph = (uint32_t)s->sph_id.size();
+  L.n_pl = (uint32_t)s->pl_id.size();
+  L.n_tri = (uint32_t)s->tri_id.size();
+  size_t off = 0;
+  L.off_sph = align16(off), off = L.off_sph + s->sph.size() * 8;
+  L.off_pl = align16(off), off = L.off_pl + s->pl.size() * 8;
+  L.off_tri = align16(off), off = L.off_tri + s->tri.size() * 8;
+  L.off_mat = align16(off), off = L.off_mat + s->mat.size() * 8;
+  L.off_sph_id = align16(off), off = L.off_sph_id + s->sph_id.size() * 4;
+  L.off_pl_id = align16(off), off = L.off_pl_id + s->pl_id.size() * 4;
+  L.off_tri_id = align16(off), off = L.off_tri_id + s->tri_id.size() * 4;
+  if (off > 0xFFFFFFF0ull) return fail(s, RTX_ERR_INVALID_ARGUMENT, "scene larger than 4 GiB is not supported");
+  L.bytes = align16(off);
+  if (L.bytes == 0) L.bytes = 16;
+  std::vector<unsigned char> blob(L.bytes, 0);
+  auto put = [&](uint32_t o, const void* src, size_t n) {
+    if (n) std::memcpy(blob.data() + o, src, n);
+  };
+  put(L.off_sph, s->sph.data(), s->sph.size() * 8);
+  put(L.off_pl, s->pl.data(), s->pl.size() * 8);
+  put(L.off_tri, s->tri.data(), s->tri.size() * 8);
+  put(L.off_mat, s->mat.data(), s->mat.size() * 8);
+  put(L.off_sph_id, s->sph_id.data(), s->sph_id.size() * 4);
+  put(L.off_pl_id, s->pl_id.data(), s->pl_id.size() * 4);
+  put(L.off_tri_id, s->tri_id.data(), s->tri_id.size() * 4);
+  RTX_CUDA_TRY(s, grow(&s->d_blob, &s->d_blob_cap, L.bytes));
+  // pageable source: the runtime stages it before returning, so `blob` may die at scope exit
+  RTX_CUDA_TRY(s, cudaMemcpyAsync(s->d_blob, blob.data(), L.bytes, cudaMemcpyHostToDevice, stream));
+  RTX_CUDA_TRY(s, cudaStreamSynchronize(stream));
+  s->layout = L;
+  s->dirty = false;
+  return RTX_OK;
+}
+
+rtx_status ensure_tables(rtx_scene* s, uint32_t width, uint32_t height, cudaStream_t stream) {
+  if (s->tab_valid && s->tab_w == width && s->tab_h == height &&
+      std::memcmp(&s->tab_fov, &s->camera.fov, 8) == 0)
+    return RTX_OK;
+  const size_t n = 2 * ((size_t)width + height);
+  std::vector<double> tab(n);
+  const double fov = s->camera.fov;
+  const double vertical_fov = (double)height / (double)width * fov;  // scene.rs:145
+  double* sin_x = tab.data();
+  double* cos_x = sin_x + width;
+  double* sin_y = cos_x + width;
+  double* cos_y = sin_y + height;
+  for (uint32_t x = 0; x < width; ++x) {
+    const double u = (double)x / (double)width;  // scene.rs:157
+    const double angle_x = fov * (u - 0.5);      // scene.rs:214
+    sin_x[x] = std::sin(angle_x);
+    cos_x[x] = std::cos(angle_x);
+  }
+  for (uint32_t y = 0; y < height; ++y) {
+    const double v = (double)y / (double)height;   // scene.rs:153
+    const double angle_y = vertical_fov * (v - 0.5);  // scene.rs:215
+    sin_y[y] = std::sin(angle_y);
+    cos_y[y] = std::cos(angle_y);
+  }
+  RTX_CUDA_TRY(s, grow(&s->d_tables, &s->d_tables_cap, n * 8));
+  RTX_CUDA_TRY(s, cudaMemcpyAsync(s->d_tables, tab.data(), n * 8, cudaMemcpyHostToDevice, stream));
+  RTX_CUDA_TRY(s, cudaStreamSynchronize(stream));
+  s->tab_w = width, s->tab_h = height, s->tab_fov = fov, s->tab_valid = true;
+  return RTX_OK;
+}
+
+static uint64_t shard_tiles(uint32_t width, uint32_t height, uint32_t index, uint32_t count) {
+  if (count == 0 || index >= count) return 0;
+  const uint64_t tiles = (uint64_t)((width + TILE - 1) / TILE) * ((height + TILE - 1) / TILE);
+  if (index >= tiles) return 0;
+  return (tiles - index + count - 1) / count;
+}
+
+// ---- small device kernels owned by the API layer ------------------------------------------------
+// ≙ the row-ordered join of scene.rs:167-169: scatter gathered per-rank tile buffers into the image.
+__global__ void deinterleave_kernel(uint32_t width, uint32_t height, uint32_t tiles_x, uint32_t count,
+                                    uint64_t slots, const double* __restrict__ g_rgb, double* __restrict__ out_rgb,
+                                    const uint32_t* __restrict__ g_ids, uint32_t* __restrict__ out_ids) {
+  const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= (uint64_t)width * height) return;
+  const uint32_t x = (uint32_t)(i % width), y = (uint32_t)(i / width);
+  const uint32_t gtile = (y / TILE) * tiles_x + (x / TILE);
+  const uint64_t src = (((uint64_t)(gtile % count) * slots + gtile / count) * TILE + (y % TILE)) * TILE + (x % TILE);
+  if (g_rgb) {
+    out_rgb[i * 3 + 0] = g_rgb[src * 3 + 0];
+    out_rgb[i * 3 + 1] = g_rgb[src * 3 + 1];
+    out_rgb[i * 3 + 2] = g_rgb[src * 3 + 2];
+  }
+  if (g_ids) out_ids[i] = g_ids[src];
+}
+
+// ≙ render_to_image, scene.rs:173-178: flip y, `* 256`, Rust's saturating `as u8` (NaN → 0).
+__device__ __forceinline__ uint8_t sat_u8(double c) {
+  const double s = fmul(c, 256.0);
+  if (!(s > 0.0)) return 0;
+  if (s >= 255.0) return 255;
+  return (uint8_t)(int)s;
+}
+__global__ void quantize_kernel(const double* __restrict__ rgb, uint32_t width, uint32_t height,
+                                uint8_t* __restrict__ out) {
+  const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= (uint64_t)width * height) return;
+  const uint32_t x = (uint32_t)(i % width), y = (uint32_t)(i / width);
+  const double* src = rgb + ((uint64_t)(height - y - 1) * width + x) * 3;
+  out[i * 3 + 0] = sat_u8(src[0]);
+  out[i * 3 + 1] = sat_u8(src[1]);
+  out[i * 3 + 2] = sat_u8(src[2]);
+}
+
+// Fills RenderParams and launches.  Counters / outputs are device pointers.
+static rtx_status render_common(rtx_scene* s, uint32_t width, uint32_t height, uint64_t seed, uint32_t flags,
+                                const rtx_shard* shard, double* d_rgb, uint32_t* d_ids,
+                                unsigned long long* d_counters, uint32_t* d_work_counter, cudaStream_t stream,
+                                uint32_t* launches) {
+  if (width == 0 || height == 0) return fail(s, RTX_ERR_INVALID_ARGUMENT, "width and height must be non-zero");
+  if ((uint64_t)width * height > 0xFFFFFFFFull) return fail(s, RTX_ERR_INVALID_ARGUMENT, "image too large");
+  const uint32_t accel = flags & RTX_ACCEL_MASK;
+  if (accel == RTX_ACCEL_MASK) return fail(s, RTX_ERR_INVALID_ARGUMENT, "invalid accel flags");
+  rtx_shard sh{0, 1};
+  if (shard) sh = *shard;
+  if (sh.count == 0 || sh.index >= sh.count) return fail(s, RTX_ERR_INVALID_ARGUMENT, "invalid shard");
+  rtx_status st = ensure_uploaded(s, stream);
+  if (st != RTX_OK) return st;
+  st = ensure_tables(s, width, height, stream);
+  if (st != RTX_OK) return st;
+
+  RenderParams p{};
+  p.cam_pos[0] = s->camera.position.x, p.cam_pos[1] = s->camera.position.y, p.cam_pos[2] = s->camera.position.z;
+  const rtx_mat3& m = s->camera.to_world_space;
+  const double rows[9] = {m.x.x, m.x.y, m.x.z, m.y.x, m.y.y, m.y.z, m.z.x, m.z.y, m.z.z};
+  std::memcpy(p.to_world, rows, sizeof(rows));
+  p.focal_length = s->config.focal_length;
+  p.focal_offset = s->config.focal_offset;
+  p.non_focal_offset = s->config.non_focal_offset;
+  p.rays_per_pixel = s->config.rays_per_pixel;
+  p.max_bounces = s->config.max_bounces;
+  p.seed = seed;
+  p.width = width, p.height = height;
+  p.sin_x = s->d_tables;
+  p.cos_x = p.sin_x + width;
+  p.sin_y = p.cos_x + width;
+  p.cos_y = p.sin_y + height;
+  p.scene_blob = s->d_blob;
+  p.layout = s->layout;
+  p.shard_index = sh.index, p.shard_count = sh.count;
+  p.tiles_x = (width + TILE - 1) / TILE, p.tiles_y = (height + TILE - 1) / TILE;
+  p.my_tiles = (uint32_t)shard_tiles(width, height, sh.index, sh.count);
+  p.compact = sh.count > 1 ? 1u : 0u;
+  p.work_counter = d_work_counter;
+  p.out_rgb = (flags & RTX_FLAG_NO_RADIANCE) ? nullptr : d_rgb;
+  p.out_ids = d_ids;
+  p.ray_counter = d_counters;
+  if (p.my_tiles == 0) return RTX_OK;
+  cudaError_t e = launch_render(p, s->sm_count, stream, launches);
+  if (e != cudaSuccess) return cuda_fail(s, e, "render kernel launch");
+  return RTX_OK;
+}
+
+}  // namespace rtx
+
+using namespace rtx;
+
+extern "C" {
+
+uint32_t rtx_abi_version(void) { return RTX_CUDA_ABI_VERSION; }
+
+const char* rtx_last_error(const rtx_scene* scene) {
+  if (scene) return scene->last_error.c_str();
+  return g_last_error.c_str();
+}
+
+int32_t rtx_device_count(void) {
+  int n = 0;
+  if (cudaGetDeviceCount(&n) != cudaSuccess) {
+    cudaGetLastError();
+    return 0;
+  }
+  return n;
+}
+
+rtx_status rtx_host_alloc(size_t bytes, void** out) {
+  if (!out) return fail(nullptr, RTX_ERR_INVALID_ARGUMENT, "null out");
+  RTX_CUDA_TRY(nullptr, cudaMallocHost(out, bytes ? bytes : 1));
+  return RTX_OK;
+}
+rtx_status rtx_host_free(void* p) {
+  if (p) RTX_CUDA_TRY(nullptr, cudaFreeHost(p));
+  return RTX_OK;
+}
+
+// ---- camera / config helpers ---------------------------------------------------------------------
+rtx_status rtx_camera_new(const rtx_vec3* position, const rtx_vec3* direction, double fov, rtx_camera* out) {
+  if (!position || !direction || !out) return fail(nullptr, RTX_ERR_INVALID_ARGUMENT, "null argument");
+  const M3 to_world = derive_to_world_space_mat(to_v3(*direction));  // camera.rs:20
+  out->fov = fov;
+  out->position = *position;
+  out->direction = *direction;
+  out->to_cam_space = from_m3(inverse(to_world));  // camera.rs:25
+  out->to_world_space = from_m3(to_world);
+  return RTX_OK;
+}
+rtx_status rtx_camera_set_direction(rtx_camera* camera, const rtx_vec3* direction) {
+  if (!camera || !direction) return fail(nullptr, RTX_ERR_INVALID_ARGUMENT, "null argument");
+  // camera.rs:35-40 — the matrices are derived from the direction stored BEFORE this call.
+  const M3 to_world = derive_to_world_space_mat(to_v3(camera->direction));
+  camera->to_cam_space = from_m3(inverse(to_world));
+  camera->to_world_space = from_m3(to_world);
+  camera->direction = *direction;
+  return RTX_OK;
+}
+rtx_status rtx_camera_to_cam_space(const rtx_camera* c, const rtx_vec3* v, rtx_vec3* out) {
+  if (!c || !v || !out) return fail(nullptr, RTX_ERR_INVALID_ARGUMENT, "null argument");
+  *out = from_v3(matvec(to_m3(c->to_cam_space), to_v3(*v) - to_v3(c->position)));  // camera.rs:51-53
+  return RTX_OK;
+}
+rtx_status rtx_camera_to_world_space(const rtx_camera* c, const rtx_vec3* v, rtx_vec3* out) {
+  if (!c || !v || !out) return fail(nullptr, RTX_ERR_INVALID_ARGUMENT, "null argument");
+  *out = from_v3(matvec(to_m3(c->to_world_space), to_v3(*v)) + to_v3(c->position));  // camera.rs:55-57
+  return RTX_OK;
+}
+rtx_status rtx_camera_rotate_to_world_space(const rtx_camera* c, const rtx_vec3* v, rtx_vec3* out) {
+  if (!c || !v || !out) return fail(nullptr, RTX_ERR_INVALID_ARGUMENT, "null argument");
+  *out = from_v3(matvec(to_m3(c->to_world_space), to_v3(*v)));  // camera.rs:65-67
+  return RTX_OK;
+}
+rtx_status rtx_config_default(rtx_config* out) {
+  if (!out) return fail(nullptr, RTX_ERR_INVALID_ARGUMENT, "null argument");
+  out->rays_per_pixel = 16;  // scene.rs:55-65
+  out->max_bounces = 10;
+  out->focal_length = 10.0;
+  out->focal_offset = 1e-4;
+  out->non_focal_offset = 1e-1;
+  return RTX_OK;
+}
+
+uint64_t rtx_stream_state(uint64_t seed, uint64_t key) { return stream_state(seed, key); }
+
+// ---- scene lifetime ------------------------------------------------------------------------------
+rtx_status rtx_scene_create(const rtx_camera* camera, const rtx_config* config, int32_t device, rtx_scene** out) {
+  if (!camera || !config || !out) return fail(nullptr, RTX_ERR_INVALID_ARGUMENT, "null argument");
+  *out = nullptr;
+  int n = 0;
+  cudaError_t e = cudaGetDeviceCount(&n);
+  if (e != cudaSuccess || n == 0) {
+    cudaGetLastError();
+    return fail(nullptr, RTX_ERR_CUDA,
+                "no CUDA device available: the rtx CUDA path has no CPU fallback (cudaGetDeviceCount failed or returned 0)");
+  }
+  if (device < 0 || device >= n) return fail(nullptr, RTX_ERR_INVALID_ARGUMENT, "device ordinal out of range");
+  RTX_CUDA_TRY(nullptr, cudaSetDevice(device));
+  rtx_scene* s = new (std::nothrow) rtx_scene();
+  if (!s) return fail(nullptr, RTX_ERR_OUT_OF_MEMORY, "host allocation failed");
+  s->device = device;
+  s->camera = *camera;
+  s->config = *config;
+  cudaDeviceProp prop{};
+  e = cudaGetDeviceProperties(&prop, device);
+  if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking);
+  if (e == cudaSuccess) e = cudaEventCreate(&s->ev0);
+  if (e == cudaSuccess) e = cudaEventCreate(&s->ev1);
+  if (e == cudaSuccess) e = cudaMalloc((void**)&s->d_work_counter, 64 * sizeof(uint32_t));
+  if (e == cudaSuccess) e = cudaMalloc((void**)&s->d_counters, 4 * sizeof(unsigned long long));
+  if (e != cudaSuccess) {
+    rtx_status st = cuda_fail(nullptr, e, "rtx_scene_create");
+    rtx_scene_destroy(s);
+    return st;
+  }
+  s->sm_count = prop.multiProcessorCount > 0 ? prop.multiProcessorCount : 148;
+  *out = s;
+  return RTX_OK;
+}
+
+rtx_status rtx_scene_destroy(rtx_scene* s) {
+  if (!s) return RTX_OK;
+  cudaSetDevice(s->device);
+  if (s->stream) cudaStreamSynchronize(s->stream);
+  cudaFree(s->d_blob);
+  cudaFree(s->d_tables);
+  cudaFree(s->d_work_counter);
+  cudaFree(s->d_counters);
+  cudaFree(s->d_rgb);
+  cudaFree(s->d_ids);
+  cudaFree(s->d_rgb8);
+  if (s->ev0) cudaEventDestroy(s->ev0);
+  if (s->ev1) cudaEventDestroy(s->ev1);
+  if (s->stream) cudaStreamDestroy(s->stream);
+  cudaGetLastError();
+  delete s;
+  return RTX_OK;
+}
+
+rtx_status rtx_scene_set_camera(rtx_scene* s, const rtx_camera* camera) {
+  if (!s || !camera) return fail(s, RTX_ERR_INVALID_ARGUMENT, "null argument");
+  std::lock_guard<std::mutex> lk(s->mu);
+  s->camera = *camera;
+  return RTX_OK;
+}
+rtx_status rtx_scene_set_config(rtx_scene* s, const rtx_config* config) {
+  if (!s || !config) return fail(s, RTX_ERR_INVALID_ARGUMENT, "null argument");
+  std::lock_guard<std::mutex> lk(s->mu);
+  s->config = *config;
+  return RTX_OK;
+}
+rtx_status rtx_scene_get_camera(const rtx_scene* s, rtx_camera* out) {
+  if (!s || !out) return fail(s, RTX_ERR_INVALID_ARGUMENT, "null argument");
+  *out = s->camera;
+  return RTX_OK;
+}
+rtx_status rtx_scene_get_config(const rtx_scene* s, rtx_config* out) {
+  if (!s || !out) return fail(s, RTX_ERR_INVALID_ARGUMENT, "null argument");
+  *out = s->config;
+  return RTX_OK;
+}
+
+static rtx_status check_add(rtx_scene* s, const void* shapes, const void* materials, uint64_t n) {
+  if (!s) return fail(s, RTX_ERR_INVALID_ARGUMENT, "null scene");
+  if (n && (!shapes || !materials)) return fail(s, RTX_ERR_INVALID_ARGUMENT, "null shapes/materials");
+  if (s->n_obj + n >= (1ull << 30)) return fail(s, RTX_ERR_INVALID_ARGUMENT, "too many objects (limit 2^30)");
+  return RTX_OK;
+}
+static void push_material(rtx_scene* s, const rtx_material& m) {
+  const size_t o = s->mat.size();
+  s->mat.resize(o + MAT_STRIDE);
+  pack_material(&m.base_color.x, &m.emission_color.x, m.roughness, &s->mat[o]);
+}
+
+rtx_status rtx_scene_add_spheres(rtx_scene* s, const rtx_sphere* shapes, const rtx_material* materials, uint64_t n) {
+  rtx_status st = check_add(s, shapes, materials, n);
+  if (st != RTX_OK) return st;
+  std::lock_guard<std::mutex> lk(s->mu);
+  s->sph.reserve(s->sph.size() + n * SPH_STRIDE);
+  for (uint64_t i = 0; i < n; ++i) {
+    const size_t o = s->sph.size();
+    s->sph.resize(o + SPH_STRIDE);
+    pack_sphere(&shapes[i].position.x, shapes[i].radius, &s->sph[o]);
+    s->sph_id.push_back((uint32_t)s->n_obj++);
+    push_material(s, materials[i]);
+  }
+  s->dirty = true;
+  return RTX_OK;
+}
+rtx_status rtx_scene_add_planes(rtx_scene* s, const rtx_plane* shapes, const rtx_material* materials, uint64_t n) {
+  rtx_status st = check_add(s, shapes, materials, n);
+  if (st != RTX_OK) return st;
+  std::lock_guard<std::mutex> lk(s->mu);
+  for (uint64_t i = 0; i < n; ++i) {
+    const size_t o = s->pl.size();
+    s->pl.resize(o + PL_STRIDE);
+    pack_plane(&shapes[i].position.x, &shapes[i].normal.x, &s->pl[o]);
+    s->pl_id.push_back((uint32_t)s->n_obj++);
+    push_material(s, materials[i]);
+  }
+  s->dirty = true;
+  return RTX_OK;
+}
+rtx_status rtx_scene_add_triangles(rtx_scene* s, const rtx_triangle* shapes, const rtx_material* materials, uint64_t n) {
+  rtx_status st = check_add(s, shapes, materials, n);
+  if (st != RTX_OK) return st;
+  std::lock_guard<std::mutex> lk(s->mu);
+  s->tri.reserve(s->tri.size() + n * TRI_STRIDE);
+  for (uint64_t i = 0; i < n; ++i) {
+    const size_t o = s->tri.size();
+    s->tri.resize(o + TRI_STRIDE);
+    pack_triangle(&shapes[i].vertices[0].x, &s->tri[o]);
+    s->tri_id.push_back((uint32_t)s->n_obj++);
+    push_material(s, materials[i]);
+  }
+  s->dirty = true;
+  return RTX_OK;
+}
+rtx_status rtx_scene_clear_objects(rtx_scene* s) {
+  if (!s) return fail(s, RTX_ERR_INVALID_ARGUMENT, "null scene");
+  std::lock_guard<std::mutex> lk(s->mu);
+  s->sph.clear(), s->pl.clear(), s->tri.clear(), s->mat.clear();
+  s->sph_id.clear(), s->pl_id.clear(), s->tri_id.clear();
+  s->n_obj = 0;
+  s->dirty = true;
+  return RTX_OK;
+}
+uint64_t rtx_scene_object_count(const rtx_scene* s) { return s ? s->n_obj : 0; }
+
+uint64_t rtx_shard_tile_count(uint32_t width, uint32_t height, uint32_t index, uint32_t count) {
+  return shard_tiles(width, height, index, count);
+}
+
+// ---- render --------------------------------------------------------------------------------------
+rtx_status rtx_scene_render_device(rtx_scene* s, uint32_t width, uint32_t height, uint64_t seed, uint32_t flags,
+                                   const rtx_shard* shard, void* d_out_rgb, void* d_out_primary_hit_id,
+                                   void* d_out_counters, void* cuda_stream) {
+  if (!s) return fail(s, RTX_ERR_INVALID_ARGUMENT, "null scene");
+  if (!d_out_rgb && !(flags & RTX_FLAG_NO_RADIANCE) && !d_out_primary_hit_id)
+    return fail(s, RTX_ERR_INVALID_ARGUMENT, "no output buffer");
+  std::lock_guard<std::mutex> lk(s->mu);
+  RTX_CUDA_TRY(s, cudaSetDevice(s->device));
+  static thread_local uint32_t slot = 0;
+  uint32_t* wc = s->d_work_counter + (slot++ & 63u);
+  uint32_t launches = 0;
+  return render_common(s, width, height, seed, flags, shard, (double*)d_out_rgb, (uint32_t*)d_out_primary_hit_id,
+                       (unsigned long long*)d_out_counters, wc, (cudaStream_t)cuda_stream, &launches);
+}
+
+rtx_status rtx_scene_render(rtx_scene* s, uint32_t width, uint32_t height, uint64_t seed, uint32_t flags,
+                            double* out_rgb, uint32_t* out_primary_hit_id, rtx_stats* out_stats) {
+  if (!s) return fail(s, RTX_ERR_INVALID_ARGUMENT, "null scene");
+  const bool want_rgb = !(flags & RTX_FLAG_NO_RADIANCE);
+  if (want_rgb && !out_rgb) return fail(s, RTX_ERR_INVALID_ARGUMENT, "out_rgb is null");
+  if (!want_rgb && !out_primary_hit_id) return fail(s, RTX_ERR_INVALID_ARGUMENT, "no output buffer");
+  const auto t0 = std::chrono::steady_clock::now();
+  std::lock_guard<std::mutex> lk(s->mu);
+  RTX_CUDA_TRY(s, cudaSetDevice(s->device));
+  const size_t npix = (size_t)width * height;
+  if (want_rgb) RTX_CUDA_TRY(s, grow(&s->d_rgb, &s->d_rgb_cap, npix * 3 * sizeof(double)));
+  if (out_primary_hit_id) RTX_CUDA_TRY(s, grow(&s->d_ids, &s->d_ids_cap, npix * sizeof(uint32_t)));
+  RTX_CUDA_TRY(s, cudaMemsetAsync(s->d_counters, 0, 4 * sizeof(unsigned long long), s->stream));
+  uint32_t launches = 0;
+  RTX_CUDA_TRY(s, cudaEventRecord(s->ev0, s->stream));
+  rtx_status st = render_common(s, width, height, seed, flags, nullptr, want_rgb ? s->d_rgb : nullptr,
+                                out_primary_hit_id ? s->d_ids : nullptr, s->d_counters, s->d_work_counter, s->stream,
+                                &launches);
+  if (st != RTX_OK) return st;
+  RTX_CUDA_TRY(s, cudaEventRecord(s->ev1, s->stream));
+  if (want_rgb)
+    RTX_CUDA_TRY(s, cudaMemcpyAsync(out_rgb, s->d_rgb, npix * 3 * sizeof(double), cudaMemcpyDeviceToHost, s->stream));
+  if (out_primary_hit_id)
+    RTX_CUDA_TRY(s, cudaMemcpyAsync(out_primary_hit_id, s->d_ids, npix * sizeof(uint32_t), cudaMemcpyDeviceToHost,
+                                    s->stream));
+  unsigned long long counters[4] = {0, 0, 0, 0};
+  RTX_CUDA_TRY(s, cudaMemcpyAsync(counters, s->d_counters, sizeof(counters), cudaMemcpyDeviceToHost, s->stream));
+  RTX_CUDA_TRY(s, cudaStreamSynchronize(s->stream));
+  if (out_stats) {
+    std::memset(out_stats, 0, sizeof(*out_stats));
+    float ms = 0.f;
+    cudaEventElapsedTime(&ms, s->ev0, s->ev1);
+    out_stats->rays = counters[0];
+    out_stats->paths = counters[1];
+    out_stats->triangle_panics = counters[2];
+    out_stats->pixels = npix;
+    out_stats->device_ms = ms;
+    out_stats->kernel_launches = launches;
+    out_stats->accel_used = RTX_ACCEL_BRUTE;
+    out_stats->prims_tested = counters[0] * s->n_obj;
+    out_stats->total_ms =
+        std::chrono::duration<float, std::milli>(std::chrono::steady_clock::now() - t0).count();
+  }
+  return RTX_OK;
+}
+
+rtx_status rtx_deinterleave_tiles(uint32_t width, uint32_t height, uint32_t count, const void* d_gathered_rgb,
+                                  void* d_out_rgb, const void* d_gathered_ids, void* d_out_ids, void* cuda_stream) {
+  if (width == 0 || height == 0 || count == 0) return fail(nullptr, RTX_ERR_INVALID_ARGUMENT, "bad geometry");
+  if ((d_gathered_rgb && !d_out_rgb) || (d_gathered_ids && !d_out_ids))
+    return fail(nullptr, RTX_ERR_INVALID_ARGUMENT, "missing output buffer");
+  const uint64_t slots = shard_tiles(width, height, 0, count);
+  const uint64_t n = (uint64_t)width * height;
+  const unsigned block = 256;
+  const unsigned grid = (unsigned)((n + block - 1) / block);
+  deinterleave_kernel<<<grid, block, 0, (cudaStream_t)cuda_stream>>>(
+      width, height, (width + TILE - 1) / TILE, count, slots, (const double*)d_gathered_rgb, (double*)d_out_rgb,
+      (const uint32_t*)d_gathered_ids, (uint32_t*)d_out_ids);
+  RTX_CUDA_TRY(nullptr, cudaGetLastError());
+  return RTX_OK;
+}
+
+rtx_status rtx_quantize_rgb8_device(const void* d_rgb, uint32_t width, uint32_t height, void* d_out_rgb8,
+                                    void* cuda_stream) {
+  if (!d_rgb || !d_out_rgb8 || width == 0 || height == 0)
+    return fail(nullptr, RTX_ERR_INVALID_ARGUMENT, "bad argument");
+  const uint64_t n = (uint64_t)width * height;
+  const unsigned block = 256;
+  quantize_kernel<<<(unsigned)((n + block - 1) / block), block, 0, (cudaStream_t)cuda_stream>>>(
+      (const double*)d_rgb, width, height, (uint8_t*)d_out_rgb8);
+  RTX_CUDA_TRY(nullptr, cudaGetLastError());
+  return RTX_OK;
+}
+
+rtx_status rtx_scene_render_to_rgb8(rtx_scene* s, uint32_t width, uint32_t height, uint64_t seed, uint32_t flags,
+                                    uint8_t* out_rgb8, rtx_stats* out_stats) {
+  if (!s || !out_rgb8) return fail(s, RTX_ERR_INVALID_ARGUMENT, "null argument");
+  if (flags & RTX_FLAG_NO_RADIANCE) return fail(s, RTX_ERR_INVALID_ARGUMENT, "rgb8 output needs radiance");
+  const auto t0 = std::chrono::steady_clock::now();
+  std::lock_guard<std::mutex> lk(s->mu);
+  RTX_CUDA_TRY(s, cudaSetDevice(s->device));
+  const size_t npix = (size_t)width * height;
+  RTX_CUDA_TRY(s, grow(&s->d_rgb, &s->d_rgb_cap, npix * 3 * sizeof(double)));
+  RTX_CUDA_TRY(s, grow(&s->d_rgb8, &s->d_rgb8_cap, npix * 3));
+  RTX_CUDA_TRY(s, cudaMemsetAsync(s->d_counters, 0, 4 * sizeof(unsigned long long), s->stream));
+  uint32_t launches = 0;
+  RTX_CUDA_TRY(s, cudaEventRecord(s->ev0, s->stream));
+  rtx_status st = render_common(s, width, height, seed, flags, nullptr, s->d_rgb, nullptr, s->d_counters,
+                                s->d_work_counter, s->stream, &launches);
+  if (st != RTX_OK) return st;
+  st = rtx_quantize_rgb8_device(s->d_rgb, width, height, s->d_rgb8, s->stream);
+  if (st != RTX_OK) return st;
+  ++launches;
+  RTX_CUDA_TRY(s, cudaEventRecord(s->ev1, s->stream));
+  RTX_CUDA_TRY(s, cudaMemcpyAsync(out_rgb8, s->d_rgb8, npix * 3, cudaMemcpyDeviceToHost, s->stream));
+  unsigned long long counters[4] = {0, 0, 0, 0};
+  RTX_CUDA_TRY(s, cudaMemcpyAsync(counters, s->d_counters, sizeof(counters), cudaMemcpyDeviceToHost, s->stream));
+  RTX_CUDA_TRY(s, cudaStreamSynchronize(s->stream));
+  if (out_stats) {
+    std::memset(out_stats, 0, sizeof(*out_stats));
+    float ms = 0.f;
+    cudaEventElapsedTime(&ms, s->ev0, s->ev1);
+    out_stats->rays = counters[0];
+    out_stats->paths = counters[1];
+    out_stats->triangle_panics = counters[2];
+    out_stats->pixels = npix;
+    out_stats->device_ms = ms;
+    out_stats->kernel_launches = launches;
+    out_stats->accel_used = RTX_ACCEL_BRUTE;
+    out_stats->prims_tested = counters[0] * s->n_obj;
+    out_stats->total_ms =
+        std::chrono::duration<float, std::milli>(std::chrono::steady_clock::now() - t0).count();
+  }
+  return RTX_OK;
+}
+
+}  // extern "C"

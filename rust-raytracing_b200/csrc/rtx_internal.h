@@ -1,0 +1,67 @@
+// rtx_internal.h — the opaque scene handle and helpers shared by the C-ABI translation units.
+#pragma once
+#include <cuda_runtime.h>
+
+#include <mutex>
+#include <string>
+#include <vector>
+
+#include "../../include/rtx_cuda.h"
+#include "rtx_render.cuh"
+
+struct rtx_scene {
+  int device = 0;
+  int sm_count = 148;
+  rtx_camera camera{};
+  rtx_config config{};
+  std::mutex mu;                 // serialises render / upload on this handle (Scene::render is &self)
+  mutable std::string last_error;
+
+  // host-side packed records (see rtx_scene.cuh); object index = insertion order across all three
+  std::vector<double> sph, pl, tri, mat;
+  std::vector<uint32_t> sph_id, pl_id, tri_id;
+  uint64_t n_obj = 0;
+  bool dirty = true;
+
+  // device copies
+  unsigned char* d_blob = nullptr;
+  size_t d_blob_cap = 0;
+  rtx::SceneLayout layout{};
+
+  // separable sin/cos tables of get_ray_dir, cached per (width, height, fov)
+  double* d_tables = nullptr;  // [sin_x W][cos_x W][sin_y H][cos_y H]
+  size_t d_tables_cap = 0;
+  uint32_t tab_w = 0, tab_h = 0;
+  double tab_fov = 0.0;
+  bool tab_valid = false;
+
+  uint32_t* d_work_counter = nullptr;
+  unsigned long long* d_counters = nullptr;  // [0] rays [1] paths [2] panics
+
+  // framebuffers owned by the host-buffer entry points
+  double* d_rgb = nullptr;
+  size_t d_rgb_cap = 0;
+  uint32_t* d_ids = nullptr;
+  size_t d_ids_cap = 0;
+  uint8_t* d_rgb8 = nullptr;
+  size_t d_rgb8_cap = 0;
+
+  cudaStream_t stream = nullptr;  // used by the blocking host-buffer entry points
+  cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+};
+
+namespace rtx {
+rtx_status fail(const rtx_scene* s, rtx_status code, const std::string& msg);
+rtx_status cuda_fail(const rtx_scene* s, cudaError_t e, const char* what);
+// Uploads the packed scene if it changed; fills s->layout.  Asynchronous on `stream`.
+rtx_status ensure_uploaded(rtx_scene* s, cudaStream_t stream);
+// Builds (or reuses) the sin/cos tables for this image size.  Asynchronous on `stream`.
+rtx_status ensure_tables(rtx_scene* s, uint32_t width, uint32_t height, cudaStream_t stream);
+cudaError_t launch_render(const RenderParams& p, int sm_count, cudaStream_t stream, uint32_t* out_launches);
+}  // namespace rtx
+
+#define RTX_CUDA_TRY(scene, expr)                                      \
+  do {                                                                 \
+    cudaError_t _e = (expr);                                           \
+    if (_e != cudaSuccess) return rtx::cuda_fail((scene), _e, #expr);  \
+  } while (0)

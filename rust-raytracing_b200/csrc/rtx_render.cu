@@ -1,0 +1,264 @@
+// rtx_render.cu — the render mega-kernel: camera-ray generation → nearest hit → shade/bounce →
+// per-pixel accumulation, fused, for sm_100a.
+//
+// Replaces the per-pixel closure of Scene::render (raytracing/scene.rs:144-170) and everything it
+// calls: render_pixel :194-212, get_ray_dir :213-222, render_ray :223-242, closest_object :243-251,
+// avg :253-259, ray_hit :260-278, random_bounce_dir :279-291.
+//
+// Shape of the kernel:
+//  * persistent CTAs (a multiple of the SM count); each WARP pulls 8×4-pixel granules from one global
+//    atomic counter, and each LANE pulls the next pixel of its warp's granule with a ballot/popc rank —
+//    so a lane whose pixel is finished never waits for its neighbours (path lengths differ per sample);
+//  * one loop iteration = one nearest-hit query per lane (a "ray" of the Mrays/s metric); lanes whose
+//    path ended regenerate a camera sample in the same iteration instead of idling;
+//  * the scene blob is staged once per CTA into shared memory with a TMA bulk copy
+//    (cp.async.bulk + mbarrier) when it fits, and read with 128-bit broadcast loads;
+//  * a pixel's samples are accumulated sequentially by the lane that owns it, in sample order, so
+//    the f64 sum is the reference's left fold (iter_ops.rs:4-8) bit for bit.
+#include <cuda_runtime.h>
+#include <math_constants.h>
+
+#include "rtx_render.cuh"
+#include "rtx_trace.cuh"
+
+namespace rtx {
+
+constexpr int RENDER_BLOCK = 256;
+constexpr uint32_t FULL = 0xFFFFFFFFu;
+
+// ---- TMA bulk copy (global → shared) with an mbarrier ------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void* p) {
+  return (uint32_t)__cvta_generic_to_shared(p);
+}
+__device__ __forceinline__ void stage_blob(unsigned char* dst, const unsigned char* src, uint32_t bytes,
+                                           uint64_t* mbar) {
+  const uint32_t bar = smem_u32(mbar);
+  if (threadIdx.x == 0) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar));
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+    asm volatile(
+        "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+            smem_u32(dst)),
+        "l"(src), "r"(bytes), "r"(bar)
+        : "memory");
+  }
+  // every thread waits for phase 0 of the barrier
+  asm volatile(
+      "{\n"
+      ".reg .pred P1;\n"
+      "WAIT_LOOP:\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 P1, [%0], 0;\n"
+      "@P1 bra DONE;\n"
+      "bra WAIT_LOOP;\n"
+      "DONE:\n"
+      "}\n" ::"r"(bar)
+      : "memory");
+}
+
+template <bool SMEM_SCENE>
+__global__ void __launch_bounds__(RENDER_BLOCK, 2) render_megakernel(const __grid_constant__ RenderParams p) {
+  extern __shared__ __align__(128) unsigned char smem_raw[];
+  const unsigned char* base = p.scene_blob;
+  if (SMEM_SCENE) {
+    uint64_t* mbar = reinterpret_cast<uint64_t*>(smem_raw);
+    unsigned char* dst = smem_raw + 128;
+    stage_blob(dst, p.scene_blob, p.layout.bytes, mbar);
+    base = dst;
+  }
+  const SceneView sc = make_view(base, p.layout);
+
+  const uint32_t lane = threadIdx.x & 31u;
+  const uint32_t lt_mask = (1u << lane) - 1u;
+
+  const V3 cam_pos = mk3(p.cam_pos[0], p.cam_pos[1], p.cam_pos[2]);
+  M3 to_world;
+  to_world.x = mk3(p.to_world[0], p.to_world[1], p.to_world[2]);
+  to_world.y = mk3(p.to_world[3], p.to_world[4], p.to_world[5]);
+  to_world.z = mk3(p.to_world[6], p.to_world[7], p.to_world[8]);
+  const uint64_t rpp = p.rays_per_pixel;
+  const uint64_t max_segments = p.max_bounces + 1ull;  // scene.rs:227
+  const uint32_t total_work = p.my_tiles * GRANS_PER_TILE;
+
+  // warp-uniform queue state
+  uint32_t g_x0 = 0, g_y0 = 0, g_w = 0, g_npix = 0, g_next = 0, g_base_out = 0, g_tx0 = 0, g_ty0 = 0;
+  bool exhausted = false;
+
+  // per-lane pixel state
+  bool have_pixel = false;
+  uint32_t out_index = 0;
+  uint64_t key_base = 0, sample = 0;
+  V3 pix_dir = mk3(0, 0, 0), focal = mk3(0, 0, 0), acc = mk3(0, 0, 0);
+  // per-lane path state (ray.rs:4-21)
+  bool alive = false;
+  V3 pos = mk3(0, 0, 0), dir = mk3(0, 0, 0), light = mk3(0, 0, 0), res = mk3(0, 0, 0);
+  uint64_t segment = 0;
+  WyRand rng;
+  rng.s = 0;
+  // counters
+  uint32_t n_rays = 0, n_paths = 0, n_panics = 0;
+
+  for (;;) {
+    // ---- 1. pixel acquisition: lanes without a pixel take the next slots of the warp's granule ----
+    uint32_t need = __ballot_sync(FULL, !have_pixel);
+    while (need != 0u && !exhausted) {
+      if (g_next >= g_npix) {
+        uint32_t w = 0;
+        if (lane == 0) w = atomicAdd(p.work_counter, 1u);
+        w = __shfl_sync(FULL, w, 0);
+        if (w >= total_work) {
+          exhausted = true;
+          break;
+        }
+        const uint32_t ltile = w / GRANS_PER_TILE, sub = w % GRANS_PER_TILE;
+        const uint32_t gtile = ltile * p.shard_count + p.shard_index;
+        const uint32_t ty = gtile / p.tiles_x, tx = gtile % p.tiles_x;
+        g_tx0 = tx * TILE;
+        g_ty0 = ty * TILE;
+        g_x0 = g_tx0 + (sub % (TILE / GRAN_W)) * GRAN_W;
+        g_y0 = g_ty0 + (sub / (TILE / GRAN_W)) * GRAN_H;
+        const uint32_t gw = g_x0 < p.width ? min(GRAN_W, p.width - g_x0) : 0u;
+        const uint32_t gh = g_y0 < p.height ? min(GRAN_H, p.height - g_y0) : 0u;
+        g_w = gw;
+        g_npix = gw * gh;
+        g_next = 0;
+        g_base_out = ltile * (TILE * TILE);
+        continue;  // re-check (granule may be empty at the image border)
+      }
+      const uint32_t slot = g_next + __popc(need & lt_mask);
+      if (!have_pixel && slot < g_npix) {
+        const uint32_t x = g_x0 + slot % g_w, y = g_y0 + slot / g_w;
+        have_pixel = true;
+        const uint32_t pixel_index = y * p.width + x;
+        out_index = p.compact ? g_base_out + (y - g_ty0) * TILE + (x - g_tx0) : pixel_index;
+        key_base = (uint64_t)pixel_index * rpp;
+        sample = 0;
+        acc = mk3(0.0, 0.0, 0.0);  // iter_ops.rs:4-8: fold starts from zeros()
+        // scene.rs:213-222 with the libm calls hoisted to the host tables
+        const V3 cam_dir = mk3(p.sin_x[x], p.sin_y[y], fmul(p.cos_x[x], p.cos_y[y]));
+        pix_dir = matvec(to_world, cam_dir);                  // camera.rs:65-67
+        focal = cam_pos + pix_dir * p.focal_length;            // scene.rs:203
+        if (p.out_ids) p.out_ids[out_index] = MISS_ID;
+        if (rpp == 0) {  // avg of an empty iterator: zeros / 0.0 = NaN (scene.rs:253-259)
+          if (p.out_rgb) {
+            const V3 px = acc / (double)rpp;
+            p.out_rgb[(size_t)out_index * 3 + 0] = px.x;
+            p.out_rgb[(size_t)out_index * 3 + 1] = px.y;
+            p.out_rgb[(size_t)out_index * 3 + 2] = px.z;
+          }
+          have_pixel = false;
+        }
+      }
+      g_next = min(g_next + (uint32_t)__popc(need), g_npix);
+      need = __ballot_sync(FULL, !have_pixel);
+    }
+    if (!__any_sync(FULL, have_pixel)) break;  // queue exhausted and every lane is done
+
+    // ---- 2. start the next camera sample (scene.rs:199-210) ----
+    if (have_pixel && !alive) {
+      rng.s = stream_state(p.seed, key_base + sample);
+      const double u0 = wy_f64(rng), u1 = wy_f64(rng), u2 = wy_f64(rng);
+      pos = cam_pos + mk3(u0, u1, u2) * p.non_focal_offset;
+      const double u3 = wy_f64(rng), u4 = wy_f64(rng), u5 = wy_f64(rng);
+      const V3 target = focal + mk3(u3, u4, u5) * p.focal_offset;
+      dir = vnorm(target - pos);
+      light = mk3(1.0, 1.0, 1.0);
+      res = mk3(0.0, 0.0, 0.0);
+      segment = 0;
+      alive = true;
+      ++n_paths;
+    }
+
+    // ---- 3. one segment of render_ray (scene.rs:227-240) ----
+    if (alive) {
+      bool end = false;
+      if (sc.n_obj == 0) {
+        end = true;  // scene.rs:224-226
+      } else {
+        const Hit h = closest_brute(sc, pos, dir, &n_panics);
+        ++n_rays;
+        if (segment == 0 && sample == 0 && p.out_ids) p.out_ids[out_index] = h.id;
+        if (h.id == MISS_ID) {
+          end = true;
+        } else {
+          pos = pos + dir * h.t;  // scene.rs:234
+          const double* m = sc.mat + (size_t)h.id * MAT_STRIDE;
+          const V3 base_color = mk3(m[0], m[1], m[2]);
+          const V3 emission = mk3(m[3], m[4], m[5]);
+          const V3 new_light = light * base_color;
+          ++segment;
+          // The bounce direction (scene.rs:275) is only consumed by a later segment.  When this was the
+          // last allowed segment (:227) or light_color is now zero (:228 breaks before the next query)
+          // nothing reads it, and the stream is private to this (pixel, sample): skip it.
+          const bool last = (segment == max_segments) ||
+                            (new_light.x == 0.0 && new_light.y == 0.0 && new_light.z == 0.0);
+          if (!last) {
+            const V3 n = normal_at(sc, h.ref, pos);
+            dir = random_bounce_dir(rng, dir, n, m[6]);
+          }
+          res = res + light * emission;  // scene.rs:276
+          light = new_light;             // scene.rs:277
+          end = last;
+        }
+      }
+      if (end) {
+        acc = acc + res;  // Sum: a + b, left to right
+        alive = false;
+        ++sample;
+        if (sample == rpp) {
+          if (p.out_rgb) {
+            const V3 px = acc / (double)rpp;  // avg: `/ length` (scene.rs:258)
+            p.out_rgb[(size_t)out_index * 3 + 0] = px.x;
+            p.out_rgb[(size_t)out_index * 3 + 1] = px.y;
+            p.out_rgb[(size_t)out_index * 3 + 2] = px.z;
+          }
+          have_pixel = false;
+        }
+      }
+    }
+  }
+
+  // ---- counters: one atomic per warp ----
+  if (p.ray_counter) {
+    unsigned long long r = n_rays, q = n_paths, e = n_panics;
+    for (int o = 16; o > 0; o >>= 1) {
+      r += __shfl_down_sync(FULL, r, o);
+      q += __shfl_down_sync(FULL, q, o);
+      e += __shfl_down_sync(FULL, e, o);
+    }
+    if (lane == 0) {
+      atomicAdd(&p.ray_counter[0], r);
+      atomicAdd(&p.ray_counter[1], q);
+      if (e) atomicAdd(&p.ray_counter[2], e);
+    }
+  }
+}
+
+// Launch helper used by the API layer.  Returns the cudaError of the launch.
+cudaError_t launch_render(const RenderParams& p, int sm_count, cudaStream_t stream, uint32_t* out_launches) {
+  constexpr uint32_t SMEM_LIMIT = 64u * 1024u;
+  const bool use_smem = p.layout.bytes > 0 && p.layout.bytes <= SMEM_LIMIT;
+  const size_t smem = use_smem ? (size_t)p.layout.bytes + 128 : 0;
+  cudaError_t e = cudaMemsetAsync(p.work_counter, 0, sizeof(uint32_t), stream);
+  if (e != cudaSuccess) return e;
+  int blocks_per_sm = 2;
+  const uint64_t total_work = (uint64_t)p.my_tiles * GRANS_PER_TILE;
+  // persistent grid: a multiple of the SM count, never more warps than granules
+  uint64_t want_blocks = (total_work + (RENDER_BLOCK / 32) - 1) / (RENDER_BLOCK / 32);
+  uint64_t grid = (uint64_t)sm_count * blocks_per_sm;
+  if (want_blocks < grid) grid = want_blocks ? want_blocks : 1;
+  if (use_smem) {
+    e = cudaFuncSetAttribute(render_megakernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    render_megakernel<true><<<(unsigned)grid, RENDER_BLOCK, smem, stream>>>(p);
+  } else {
+    render_megakernel<false><<<(unsigned)grid, RENDER_BLOCK, 0, stream>>>(p);
+  }
+  if (out_launches) *out_launches += 1;
+  return cudaGetLastError();
+}
+
+}  // namespace rtx

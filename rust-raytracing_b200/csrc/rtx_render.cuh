@@ -1,0 +1,44 @@
+// rtx_render.cuh — launch parameters shared between the API layer and the render kernels.
+#pragma once
+#include "rtx_scene.cuh"
+
+namespace rtx {
+
+// Work granule pulled from the atomic queue: an 8×4-pixel block inside an RTX_TILE×RTX_TILE tile.
+// Tiles (16×16) are the multi-GPU ownership unit; granules keep the queue fine enough for a short tail.
+constexpr uint32_t TILE = 16;
+constexpr uint32_t GRAN_W = 8, GRAN_H = 4;
+constexpr uint32_t GRANS_PER_TILE = (TILE / GRAN_W) * (TILE / GRAN_H);  // 8
+constexpr uint32_t GRAN_PIXELS = GRAN_W * GRAN_H;                       // 32
+
+struct RenderParams {
+  // camera (camera.rs:7-15) and config (scene.rs:16-28)
+  double cam_pos[3];
+  double to_world[9];  // rows of Camera.to_world_space
+  double focal_length, focal_offset, non_focal_offset;
+  uint64_t rays_per_pixel;
+  uint64_t max_bounces;
+  uint64_t seed;
+  uint32_t width, height;
+  // get_ray_dir (scene.rs:213-222) is separable: sin/cos of the column angle and of the row angle,
+  // computed on the host with the same libm the reference uses.
+  const double* sin_x;  // [width]
+  const double* cos_x;  // [width]
+  const double* sin_y;  // [height]
+  const double* cos_y;  // [height]
+  // scene
+  const unsigned char* scene_blob;
+  SceneLayout layout;
+  // image shard
+  uint32_t shard_index, shard_count;
+  uint32_t tiles_x, tiles_y;
+  uint32_t my_tiles;    // tiles owned by this shard
+  uint32_t compact;     // 1: outputs use the compact per-shard tile layout
+  uint32_t* work_counter;  // zeroed before launch
+  // outputs
+  double* out_rgb;                  // may be null (RTX_FLAG_NO_RADIANCE)
+  uint32_t* out_ids;                // may be null
+  unsigned long long* ray_counter;  // [0] rays, [1] paths, [2] triangle panics; may be null
+};
+
+}  // namespace rtx
