@@ -84,6 +84,7 @@ typedef struct {
   uint32_t accel_used;      /* RTX_ACCEL_BRUTE or RTX_ACCEL_LBVH                                     */
   uint64_t nodes_visited;   /* LBVH: internal nodes popped (0 for brute force)                       */
   uint64_t prims_tested;    /* primitive distance evaluations                                        */
+  uint64_t hits;            /* queries that hit an object (rays - hits = misses)                     */
 } rtx_stats;
 
 /* Image shard for multi-GPU rendering: the image is cut into RTX_TILE×RTX_TILE pixel tiles numbered
@@ -134,7 +135,7 @@ rtx_status rtx_scene_render(rtx_scene* scene, uint32_t width, uint32_t height, u
  * d_out_primary_hit_id use the full-image layout above.  With count > 1 they are COMPACT: local tile
  * j (global tile j*count + index) occupies [j][RTX_TILE][RTX_TILE][3] doubles / [j][RTX_TILE][RTX_TILE]
  * ids — equal-sized per-rank buffers that a gather concatenates (see rtx_deinterleave_tiles).
- * d_out_counters: uint64[3] device counters {rays, paths, triangle_panics} to accumulate into, or
+ * d_out_counters: uint64[4] device counters {rays, paths, triangle_panics, hits} to accumulate into, or
  * NULL.  Time it with events on your stream.                                                       */
 rtx_status rtx_scene_render_device(rtx_scene* scene, uint32_t width, uint32_t height, uint64_t seed, uint32_t flags,
                                    const rtx_shard* shard, void* d_out_rgb, void* d_out_primary_hit_id,

@@ -503,6 +503,7 @@ rtx_status rtx_scene_render(rtx_scene* s, uint32_t width, uint32_t height, uint6
     out_stats->rays = counters[0];
     out_stats->paths = counters[1];
     out_stats->triangle_panics = counters[2];
+    out_stats->hits = counters[3];
     out_stats->pixels = npix;
     out_stats->device_ms = ms;
     out_stats->kernel_launches = launches;
@@ -573,6 +574,7 @@ rtx_status rtx_scene_render_to_rgb8(rtx_scene* s, uint32_t width, uint32_t heigh
     out_stats->rays = counters[0];
     out_stats->paths = counters[1];
     out_stats->triangle_panics = counters[2];
+    out_stats->hits = counters[3];
     out_stats->pixels = npix;
     out_stats->device_ms = ms;
     out_stats->kernel_launches = launches;

@@ -99,7 +99,7 @@ __global__ void __launch_bounds__(RENDER_BLOCK, 2) render_megakernel(const __gri
   WyRand rng;
   rng.s = 0;
   // counters
-  uint32_t n_rays = 0, n_paths = 0, n_panics = 0;
+  uint32_t n_rays = 0, n_paths = 0, n_panics = 0, n_hits = 0;
 
   for (;;) {
     // ---- 1. pixel acquisition: lanes without a pixel take the next slots of the warp's granule ----
@@ -185,6 +185,7 @@ __global__ void __launch_bounds__(RENDER_BLOCK, 2) render_megakernel(const __gri
           end = true;
         } else {
           pos = pos + dir * h.t;  // scene.rs:234
+          ++n_hits;
           const double* m = sc.mat + (size_t)h.id * MAT_STRIDE;
           const V3 base_color = mk3(m[0], m[1], m[2]);
           const V3 emission = mk3(m[3], m[4], m[5]);
@@ -223,16 +224,18 @@ __global__ void __launch_bounds__(RENDER_BLOCK, 2) render_megakernel(const __gri
 
   // ---- counters: one atomic per warp ----
   if (p.ray_counter) {
-    unsigned long long r = n_rays, q = n_paths, e = n_panics;
+    unsigned long long r = n_rays, q = n_paths, e = n_panics, hh = n_hits;
     for (int o = 16; o > 0; o >>= 1) {
       r += __shfl_down_sync(FULL, r, o);
       q += __shfl_down_sync(FULL, q, o);
       e += __shfl_down_sync(FULL, e, o);
+      hh += __shfl_down_sync(FULL, hh, o);
     }
     if (lane == 0) {
       atomicAdd(&p.ray_counter[0], r);
       atomicAdd(&p.ray_counter[1], q);
       if (e) atomicAdd(&p.ray_counter[2], e);
+      atomicAdd(&p.ray_counter[3], hh);
     }
   }
 }

@@ -38,7 +38,7 @@ struct RenderParams {
   // outputs
   double* out_rgb;                  // may be null (RTX_FLAG_NO_RADIANCE)
   uint32_t* out_ids;                // may be null
-  unsigned long long* ray_counter;  // [0] rays, [1] paths, [2] triangle panics; may be null
+  unsigned long long* ray_counter;  // [0] rays, [1] paths, [2] triangle panics, [3] hits; may be null
 };
 
 }  // namespace rtx

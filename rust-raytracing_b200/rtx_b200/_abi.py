@@ -49,7 +49,7 @@ class Stats(C.Structure):
     _fields_ = [("rays", C.c_uint64), ("paths", C.c_uint64), ("pixels", C.c_uint64),
                 ("triangle_panics", C.c_uint64), ("device_ms", C.c_float), ("total_ms", C.c_float),
                 ("kernel_launches", C.c_uint32), ("accel_used", C.c_uint32),
-                ("nodes_visited", C.c_uint64), ("prims_tested", C.c_uint64)]
+                ("nodes_visited", C.c_uint64), ("prims_tested", C.c_uint64), ("hits", C.c_uint64)]
 
 
 class Shard(C.Structure):

@@ -1,0 +1,102 @@
+"""CPU, world_size 2, gloo: the host logic of the multi-GPU path — tile ownership, compact shard layout,
+gather to rank 0 — without a GPU.  Pixels come from the oracle (cut into each rank's compact tiles by a
+test-local helper); the product's de-interleave is a CUDA kernel, so its index math is checked here
+against a numpy restatement, and byte-for-byte on the GPU in test_gpu_render.py / test_dist_gpu.py."""
+import os
+import sys
+
+import numpy as np
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+T = 16
+
+
+def compact_tiles(img, rank, world, slots):
+    """Full image [h][w][c] → rank's compact buffer [slots][16][16][c] (zero padded)."""
+    h, w = img.shape[:2]
+    tx_n, ty_n = (w + T - 1) // T, (h + T - 1) // T
+    out = np.zeros((slots, T, T) + img.shape[2:], dtype=img.dtype)
+    for gt in range(rank, tx_n * ty_n, world):
+        ty, tx = divmod(gt, tx_n)
+        blk = img[ty * T:(ty + 1) * T, tx * T:(tx + 1) * T]
+        out[gt // world, :blk.shape[0], :blk.shape[1]] = blk
+    return out
+
+
+def deinterleave_numpy(g, w, h, world):
+    """Restates rtx_deinterleave_tiles' index math: gathered [world][slots][16][16][c] → [h][w][c]."""
+    tx_n = (w + T - 1) // T
+    out = np.empty((h, w) + g.shape[4:], dtype=g.dtype)
+    for y in range(h):
+        for x in range(w):
+            gt = (y // T) * tx_n + (x // T)
+            out[y, x] = g[gt % world, gt // world, y % T, x % T]
+    return out
+
+
+def _worker(rank, world, port, w, h, q):
+    sys.path.insert(0, ROOT)
+    sys.path.insert(0, os.path.join(ROOT, "rust-raytracing_b200"))
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        from oracle import oracle
+        from rtx_b200 import dist as rdist
+        from rtx_b200 import scenes, shard_tile_count
+        sc = scenes.sphere_demo(rays_per_pixel=1, max_bounces=2)
+        full = oracle.render_scene(sc, w, h, seed=4, nthreads=2)
+        slots = rdist.shard_slots(w, h, world)
+        mine = int(shard_tile_count(w, h, rank, world))
+        assert mine <= slots
+        rgb_c = torch.from_numpy(compact_tiles(full["rgb"], rank, world, slots))
+        ids_c = torch.from_numpy(compact_tiles(full["ids"].view(np.int32), rank, world, slots))
+        g_rgb = rdist.gather_shards(rgb_c)
+        g_ids = rdist.gather_shards(ids_c)
+        if rank == 0:
+            assert tuple(g_rgb.shape) == (world, slots, T, T, 3)
+            img = deinterleave_numpy(g_rgb.numpy(), w, h, world)
+            ids = deinterleave_numpy(g_ids.numpy(), w, h, world)
+            ok = img.tobytes() == full["rgb"].tobytes() and np.array_equal(ids.view(np.uint32), full["ids"])
+            try:
+                rdist.deinterleave(w, h, world, g_rgb, g_ids)
+                ok = False  # must refuse CPU tensors: no CPU fallback
+            except RuntimeError:
+                pass
+            q.put(ok)
+        else:
+            assert g_rgb is None and g_ids is None
+        dist.barrier()
+    finally:
+        dist.destroy_process_group()
+
+
+def test_two_rank_gather_reassembles_the_image():
+    import socket
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    port = s.getsockname()[1]
+    s.close()
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    procs = [ctx.Process(target=_worker, args=(r, 2, port, 72, 40, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    for p in procs:
+        p.join(240)
+        assert p.exitcode == 0
+    assert q.get(timeout=5) is True
+
+
+def test_tile_ownership_is_a_partition():
+    sys.path.insert(0, os.path.join(ROOT, "rust-raytracing_b200"))
+    from rtx_b200 import shard_tile_count
+    for (w, h) in ((72, 40), (1920, 1080), (3840, 2160), (17, 16)):
+        tiles = ((w + T - 1) // T) * ((h + T - 1) // T)
+        for world in (1, 2, 4, 8):
+            owned = [len(range(r, tiles, world)) for r in range(world)]
+            assert owned == [int(shard_tile_count(w, h, r, world)) for r in range(world)]
+            assert sum(owned) == tiles
