@@ -86,13 +86,13 @@ def test_empty_scene_zero_spp_and_depth_limits(rtx, oracle, gpu):
 def test_triangles_planes_spheres_scene(rtx, oracle, gpu):
     from rtx_b200 import Camera, Config, Material, Object, Plane, Scene, Sphere, Triangle
     sc = Scene(Config().with_rays_per_pixel(2).with_max_bounces(4), Camera((0, 0, 1), (1, 0, 0.2), 1.2))
-    sc.add_object(Object(Triangle([(4, -2, 3), (4, 2, 3), (8, 0, 3.5)]), Material((0.7, 0.7, 0.2), (0, 0, 0), 0.3)))
+    sc.add_object(Object(Triangle([(4, -2, 3), (8, 0, 3.5), (4, 2, 3)]), Material((0.7, 0.7, 0.2), (0, 0, 0), 0.3)))
     sc.add_object(Object(Plane((0, 0, 0), (0, 0, 1)), Material.colored((0.5, 0.5, 0.5))))
-    sc.add_object(Object(Triangle([(5, -3, 0.1), (7, 1, 2), (5, 3, 0.1)]), Material((0.2, 0.7, 0.9), (0, 0, 0), 1.0)))
+    sc.add_object(Object(Triangle([(5, -3, 0.1), (5, 3, 0.1), (7, 1, 2)]), Material((0.2, 0.7, 0.9), (0, 0, 0), 1.0)))
     sc.add_object(Object(Sphere((6, 0, 9), 4), Material.light((3, 3, 3))))
     sc.add_object(Object(Triangle([(0, 0, 5), (0, 0, 5), (0, 4, 5)]), Material.mirror()))  # degenerate: never hit
     rgb, ids, ref, err = _compare(rtx, oracle, sc, 320, 200, seed=9)
-    assert len(np.unique(ids)) >= 4 and sc.last_stats.triangle_panics == ref["panics"] == 0
+    assert {0, 1, 2}.issubset(set(np.unique(ids).tolist())) and sc.last_stats.triangle_panics == ref["panics"] == 0
 
 
 def test_small_terrain_brute_force(rtx, oracle, gpu):
