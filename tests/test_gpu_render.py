@@ -83,6 +83,25 @@ def test_empty_scene_zero_spp_and_depth_limits(rtx, oracle, gpu):
         _compare(rtx, oracle, sc, 96, 64, seed=3)
 
 
+def _compare_triangle_scene(rtx, oracle, sc, w, h, seed):
+    """Triangle scenes: primary hit IDs stay bit-exact, but radiance is only statistically comparable.
+    A ray leaving a triangle re-tests that triangle with |t| = |n.(v0-pos) / (d.n)| (the abs() of
+    triangle.rs:118), i.e. rounding noise ~1e-16 that is a self-hit whenever it is not exactly 0.  Whether
+    it is exactly 0 depends on the last bit of the bounce direction, and the device sin/cos (CUDA) and the
+    oracle's (glibc, itself ifunc/FMA dependent) differ by <= 2 ulp in ~15 % of draws.  So a handful of
+    paths per 10^5 take a different number of self-hits.  Gates here: ids exact; ray count within 0.1 %;
+    PSNR >= 60 dB (north_star's N-spp gate); mean |err| small."""
+    rgb, ids = sc.render(w, h, seed=seed, want_ids=True)
+    ref = oracle.render_scene(sc, w, h, seed=seed)
+    assert np.array_equal(ids, ref["ids"]), f"{(ids != ref['ids']).sum()} primary hit ids differ"
+    assert abs(int(sc.last_stats.rays) - int(ref["rays"])) <= 1e-3 * ref["rays"], (sc.last_stats.rays, ref["rays"])
+    differing = float(np.mean(np.any(rgb != ref["rgb"], axis=2)))
+    p = psnr(rgb, ref["rgb"])
+    print(f"triangle scene: pixels differing {differing:.2e}, PSNR {p:.1f} dB, rays {sc.last_stats.rays} vs {ref['rays']}")
+    assert differing <= 2e-3 and p >= PSNR_MIN
+    return rgb, ids, ref
+
+
 def test_triangles_planes_spheres_scene(rtx, oracle, gpu):
     from rtx_b200 import Camera, Config, Material, Object, Plane, Scene, Sphere, Triangle
     sc = Scene(Config().with_rays_per_pixel(2).with_max_bounces(4), Camera((0, 0, 1), (1, 0, 0.2), 1.2))
@@ -91,15 +110,18 @@ def test_triangles_planes_spheres_scene(rtx, oracle, gpu):
     sc.add_object(Object(Triangle([(5, -3, 0.1), (5, 3, 0.1), (7, 1, 2)]), Material((0.2, 0.7, 0.9), (0, 0, 0), 1.0)))
     sc.add_object(Object(Sphere((6, 0, 9), 4), Material.light((3, 3, 3))))
     sc.add_object(Object(Triangle([(0, 0, 5), (0, 0, 5), (0, 4, 5)]), Material.mirror()))  # degenerate: never hit
-    rgb, ids, ref, err = _compare(rtx, oracle, sc, 320, 200, seed=9)
+    rgb, ids, ref = _compare_triangle_scene(rtx, oracle, sc, 320, 200, seed=9)
     assert {0, 1, 2}.issubset(set(np.unique(ids).tolist())) and sc.last_stats.triangle_panics == ref["panics"] == 0
+    # with max_bounces = 0 there is no bounce, hence no libm step: everything is bit-exact again
+    sc.config = sc.config.with_max_bounces(0)
+    _compare(rtx, oracle, sc, 320, 200, seed=9, spp_tol=0.0)
 
 
 def test_small_terrain_brute_force(rtx, oracle, gpu):
     """S3's generator at a small grid (2 x 24^2 triangles + light): brute force vs oracle, all gates."""
     from rtx_b200 import scenes
     sc = scenes.terrain(grid=25, rays_per_pixel=1, max_bounces=4)
-    rgb, ids, ref, err = _compare(rtx, oracle, sc, 160, 90, seed=1)
+    rgb, ids, ref = _compare_triangle_scene(rtx, oracle, sc, 160, 90, seed=1)
     assert (ids != rtx.MISS_ID).mean() > 0.3
 
 
