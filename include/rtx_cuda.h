@@ -135,7 +135,7 @@ rtx_status rtx_scene_render(rtx_scene* scene, uint32_t width, uint32_t height, u
  * d_out_primary_hit_id use the full-image layout above.  With count > 1 they are COMPACT: local tile
  * j (global tile j*count + index) occupies [j][RTX_TILE][RTX_TILE][3] doubles / [j][RTX_TILE][RTX_TILE]
  * ids — equal-sized per-rank buffers that a gather concatenates (see rtx_deinterleave_tiles).
- * d_out_counters: uint64[4] device counters {rays, paths, triangle_panics, hits} to accumulate into, or
+ * d_out_counters: uint64[8] device counters {rays, paths, triangle_panics, hits, nodes_visited, prims_tested, -, -} to accumulate into, or
  * NULL.  Time it with events on your stream.                                                       */
 rtx_status rtx_scene_render_device(rtx_scene* scene, uint32_t width, uint32_t height, uint64_t seed, uint32_t flags,
                                    const rtx_shard* shard, void* d_out_rgb, void* d_out_primary_hit_id,

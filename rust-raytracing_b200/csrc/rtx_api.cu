@@ -176,6 +176,17 @@ __global__ void quantize_kernel(const double* __restrict__ rgb, uint32_t width, 
   out[i * 3 + 2] = sat_u8(src[2]);
 }
 
+// RTX_ACCEL_AUTO: the O(N) scan while the whole scene fits the kernel's shared-memory stage and is small;
+// the LBVH above that.  Planes never enter a tree, so a planes-only scene is always scanned.
+uint32_t choose_accel(const rtx_scene* s, uint32_t flags) {
+  const uint32_t a = flags & RTX_ACCEL_MASK;
+  const size_t boxed = s->sph_id.size() + s->tri_id.size();
+  if (boxed == 0) return RTX_ACCEL_BRUTE;
+  if (a == RTX_ACCEL_BRUTE) return RTX_ACCEL_BRUTE;
+  if (a == RTX_ACCEL_LBVH) return RTX_ACCEL_LBVH;
+  return boxed > 48 ? RTX_ACCEL_LBVH : RTX_ACCEL_BRUTE;
+}
+
 // Fills RenderParams and launches.  Counters / outputs are device pointers.
 static rtx_status render_common(rtx_scene* s, uint32_t width, uint32_t height, uint64_t seed, uint32_t flags,
                                 const rtx_shard* shard, double* d_rgb, uint32_t* d_ids,
@@ -192,6 +203,11 @@ static rtx_status render_common(rtx_scene* s, uint32_t width, uint32_t height, u
   if (st != RTX_OK) return st;
   st = ensure_tables(s, width, height, stream);
   if (st != RTX_OK) return st;
+  const bool use_bvh = choose_accel(s, flags) == RTX_ACCEL_LBVH;
+  if (use_bvh) {
+    st = ensure_lbvh(s, stream);
+    if (st != RTX_OK) return st;
+  }
 
   RenderParams p{};
   p.cam_pos[0] = s->camera.position.x, p.cam_pos[1] = s->camera.position.y, p.cam_pos[2] = s->camera.position.z;
@@ -211,6 +227,11 @@ static rtx_status render_common(rtx_scene* s, uint32_t width, uint32_t height, u
   p.cos_y = p.sin_y + height;
   p.scene_blob = s->d_blob;
   p.layout = s->layout;
+  p.use_bvh = use_bvh ? 1u : 0u;
+  for (int k = 0; k < 4; ++k) {
+    p.bvh.nodes[k] = use_bvh ? s->d_bvh[k] : nullptr;
+    p.bvh.root[k] = use_bvh ? s->bvh_root[k] : BVH_END;
+  }
   p.shard_index = sh.index, p.shard_count = sh.count;
   p.tiles_x = (width + TILE - 1) / TILE, p.tiles_y = (height + TILE - 1) / TILE;
   p.my_tiles = (uint32_t)shard_tiles(width, height, sh.index, sh.count);
@@ -328,7 +349,7 @@ rtx_status rtx_scene_create(const rtx_camera* camera, const rtx_config* config, 
   if (e == cudaSuccess) e = cudaEventCreate(&s->ev0);
   if (e == cudaSuccess) e = cudaEventCreate(&s->ev1);
   if (e == cudaSuccess) e = cudaMalloc((void**)&s->d_work_counter, 64 * sizeof(uint32_t));
-  if (e == cudaSuccess) e = cudaMalloc((void**)&s->d_counters, 4 * sizeof(unsigned long long));
+  if (e == cudaSuccess) e = cudaMalloc((void**)&s->d_counters, 8 * sizeof(unsigned long long));
   if (e != cudaSuccess) {
     rtx_status st = cuda_fail(nullptr, e, "rtx_scene_create");
     rtx_scene_destroy(s);
@@ -343,6 +364,7 @@ rtx_status rtx_scene_destroy(rtx_scene* s) {
   if (!s) return RTX_OK;
   cudaSetDevice(s->device);
   if (s->stream) cudaStreamSynchronize(s->stream);
+  free_lbvh(s);
   cudaFree(s->d_blob);
   cudaFree(s->d_tables);
   cudaFree(s->d_work_counter);
@@ -406,6 +428,7 @@ rtx_status rtx_scene_add_spheres(rtx_scene* s, const rtx_sphere* shapes, const r
     push_material(s, materials[i]);
   }
   s->dirty = true;
+  s->bvh_valid = false;
   return RTX_OK;
 }
 rtx_status rtx_scene_add_planes(rtx_scene* s, const rtx_plane* shapes, const rtx_material* materials, uint64_t n) {
@@ -420,6 +443,7 @@ rtx_status rtx_scene_add_planes(rtx_scene* s, const rtx_plane* shapes, const rtx
     push_material(s, materials[i]);
   }
   s->dirty = true;
+  s->bvh_valid = false;
   return RTX_OK;
 }
 rtx_status rtx_scene_add_triangles(rtx_scene* s, const rtx_triangle* shapes, const rtx_material* materials, uint64_t n) {
@@ -431,19 +455,22 @@ rtx_status rtx_scene_add_triangles(rtx_scene* s, const rtx_triangle* shapes, con
     const size_t o = s->tri.size();
     s->tri.resize(o + TRI_STRIDE);
     pack_triangle(&shapes[i].vertices[0].x, &s->tri[o]);
+    s->tri_raw.insert(s->tri_raw.end(), &shapes[i].vertices[0].x, &shapes[i].vertices[0].x + 9);
     s->tri_id.push_back((uint32_t)s->n_obj++);
     push_material(s, materials[i]);
   }
   s->dirty = true;
+  s->bvh_valid = false;
   return RTX_OK;
 }
 rtx_status rtx_scene_clear_objects(rtx_scene* s) {
   if (!s) return fail(s, RTX_ERR_INVALID_ARGUMENT, "null scene");
   std::lock_guard<std::mutex> lk(s->mu);
-  s->sph.clear(), s->pl.clear(), s->tri.clear(), s->mat.clear();
+  s->sph.clear(), s->pl.clear(), s->tri.clear(), s->mat.clear(), s->tri_raw.clear();
   s->sph_id.clear(), s->pl_id.clear(), s->tri_id.clear();
   s->n_obj = 0;
   s->dirty = true;
+  s->bvh_valid = false;
   return RTX_OK;
 }
 uint64_t rtx_scene_object_count(const rtx_scene* s) { return s ? s->n_obj : 0; }
@@ -480,8 +507,9 @@ rtx_status rtx_scene_render(rtx_scene* s, uint32_t width, uint32_t height, uint6
   const size_t npix = (size_t)width * height;
   if (want_rgb) RTX_CUDA_TRY(s, grow(&s->d_rgb, &s->d_rgb_cap, npix * 3 * sizeof(double)));
   if (out_primary_hit_id) RTX_CUDA_TRY(s, grow(&s->d_ids, &s->d_ids_cap, npix * sizeof(uint32_t)));
-  RTX_CUDA_TRY(s, cudaMemsetAsync(s->d_counters, 0, 4 * sizeof(unsigned long long), s->stream));
+  RTX_CUDA_TRY(s, cudaMemsetAsync(s->d_counters, 0, 8 * sizeof(unsigned long long), s->stream));
   uint32_t launches = 0;
+  const bool had_bvh = s->bvh_valid;
   RTX_CUDA_TRY(s, cudaEventRecord(s->ev0, s->stream));
   rtx_status st = render_common(s, width, height, seed, flags, nullptr, want_rgb ? s->d_rgb : nullptr,
                                 out_primary_hit_id ? s->d_ids : nullptr, s->d_counters, s->d_work_counter, s->stream,
@@ -493,10 +521,11 @@ rtx_status rtx_scene_render(rtx_scene* s, uint32_t width, uint32_t height, uint6
   if (out_primary_hit_id)
     RTX_CUDA_TRY(s, cudaMemcpyAsync(out_primary_hit_id, s->d_ids, npix * sizeof(uint32_t), cudaMemcpyDeviceToHost,
                                     s->stream));
-  unsigned long long counters[4] = {0, 0, 0, 0};
+  unsigned long long counters[8] = {0, 0, 0, 0, 0, 0, 0, 0};
   RTX_CUDA_TRY(s, cudaMemcpyAsync(counters, s->d_counters, sizeof(counters), cudaMemcpyDeviceToHost, s->stream));
   RTX_CUDA_TRY(s, cudaStreamSynchronize(s->stream));
   if (out_stats) {
+    const uint32_t build_launches = (!had_bvh && s->bvh_valid) ? s->bvh_build_launches : 0u;
     std::memset(out_stats, 0, sizeof(*out_stats));
     float ms = 0.f;
     cudaEventElapsedTime(&ms, s->ev0, s->ev1);
@@ -507,8 +536,10 @@ rtx_status rtx_scene_render(rtx_scene* s, uint32_t width, uint32_t height, uint6
     out_stats->pixels = npix;
     out_stats->device_ms = ms;
     out_stats->kernel_launches = launches;
-    out_stats->accel_used = RTX_ACCEL_BRUTE;
-    out_stats->prims_tested = counters[0] * s->n_obj;
+    out_stats->accel_used = choose_accel(s, flags);
+    out_stats->nodes_visited = counters[4];
+    out_stats->prims_tested = counters[5];
+    if (out_stats->accel_used == RTX_ACCEL_LBVH) out_stats->kernel_launches += build_launches;
     out_stats->total_ms =
         std::chrono::duration<float, std::milli>(std::chrono::steady_clock::now() - t0).count();
   }
@@ -553,8 +584,9 @@ rtx_status rtx_scene_render_to_rgb8(rtx_scene* s, uint32_t width, uint32_t heigh
   const size_t npix = (size_t)width * height;
   RTX_CUDA_TRY(s, grow(&s->d_rgb, &s->d_rgb_cap, npix * 3 * sizeof(double)));
   RTX_CUDA_TRY(s, grow(&s->d_rgb8, &s->d_rgb8_cap, npix * 3));
-  RTX_CUDA_TRY(s, cudaMemsetAsync(s->d_counters, 0, 4 * sizeof(unsigned long long), s->stream));
+  RTX_CUDA_TRY(s, cudaMemsetAsync(s->d_counters, 0, 8 * sizeof(unsigned long long), s->stream));
   uint32_t launches = 0;
+  const bool had_bvh = s->bvh_valid;
   RTX_CUDA_TRY(s, cudaEventRecord(s->ev0, s->stream));
   rtx_status st = render_common(s, width, height, seed, flags, nullptr, s->d_rgb, nullptr, s->d_counters,
                                 s->d_work_counter, s->stream, &launches);
@@ -564,10 +596,11 @@ rtx_status rtx_scene_render_to_rgb8(rtx_scene* s, uint32_t width, uint32_t heigh
   ++launches;
   RTX_CUDA_TRY(s, cudaEventRecord(s->ev1, s->stream));
   RTX_CUDA_TRY(s, cudaMemcpyAsync(out_rgb8, s->d_rgb8, npix * 3, cudaMemcpyDeviceToHost, s->stream));
-  unsigned long long counters[4] = {0, 0, 0, 0};
+  unsigned long long counters[8] = {0, 0, 0, 0, 0, 0, 0, 0};
   RTX_CUDA_TRY(s, cudaMemcpyAsync(counters, s->d_counters, sizeof(counters), cudaMemcpyDeviceToHost, s->stream));
   RTX_CUDA_TRY(s, cudaStreamSynchronize(s->stream));
   if (out_stats) {
+    const uint32_t build_launches = (!had_bvh && s->bvh_valid) ? s->bvh_build_launches : 0u;
     std::memset(out_stats, 0, sizeof(*out_stats));
     float ms = 0.f;
     cudaEventElapsedTime(&ms, s->ev0, s->ev1);
@@ -578,8 +611,10 @@ rtx_status rtx_scene_render_to_rgb8(rtx_scene* s, uint32_t width, uint32_t heigh
     out_stats->pixels = npix;
     out_stats->device_ms = ms;
     out_stats->kernel_launches = launches;
-    out_stats->accel_used = RTX_ACCEL_BRUTE;
-    out_stats->prims_tested = counters[0] * s->n_obj;
+    out_stats->accel_used = choose_accel(s, flags);
+    out_stats->nodes_visited = counters[4];
+    out_stats->prims_tested = counters[5];
+    if (out_stats->accel_used == RTX_ACCEL_LBVH) out_stats->kernel_launches += build_launches;
     out_stats->total_ms =
         std::chrono::duration<float, std::milli>(std::chrono::steady_clock::now() - t0).count();
   }

@@ -3,11 +3,12 @@
 #include <math_constants.h>
 
 #include "rtx_internal.h"
+#include "rtx_lbvh.cuh"
 #include "rtx_trace.cuh"
 
 namespace rtx {
 
-__global__ void closest_kernel(const unsigned char* blob, SceneLayout L, const double* __restrict__ rays, uint64_t n,
+__global__ void closest_kernel(const unsigned char* blob, SceneLayout L, BvhView bv, int use_bvh, const double* __restrict__ rays, uint64_t n,
                                double* __restrict__ out_t, uint32_t* __restrict__ out_id) {
   const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
@@ -15,7 +16,9 @@ __global__ void closest_kernel(const unsigned char* blob, SceneLayout L, const d
   const V3 pos = mk3(rays[i * 6 + 0], rays[i * 6 + 1], rays[i * 6 + 2]);
   const V3 dir = mk3(rays[i * 6 + 3], rays[i * 6 + 4], rays[i * 6 + 5]);
   uint32_t panics = 0;
-  const Hit h = closest_brute(sc, pos, dir, &panics);
+  TraversalCounters tc;
+  tc.nodes = 0, tc.prims = 0;
+  const Hit h = use_bvh ? closest_lbvh(sc, bv, pos, dir, &panics, tc) : closest_brute(sc, pos, dir, &panics);
   out_id[i] = h.id;
   out_t[i] = h.id == MISS_ID ? 0.0 : h.t;
 }
@@ -89,11 +92,18 @@ extern "C" {
 rtx_status rtx_debug_closest_object(rtx_scene* s, uint32_t flags, const double* rays, uint64_t n, double* out_t,
                                     uint32_t* out_id) {
   if (!s || !rays || !out_t || !out_id) return fail(s, RTX_ERR_INVALID_ARGUMENT, "null argument");
-  (void)flags;
   std::lock_guard<std::mutex> lk(s->mu);
   RTX_CUDA_TRY(s, cudaSetDevice(s->device));
   rtx_status st = ensure_uploaded(s, s->stream);
   if (st != RTX_OK) return st;
+  const bool use_bvh = choose_accel(s, flags) == RTX_ACCEL_LBVH;
+  BvhView bv{};
+  for (int k = 0; k < 4; ++k) bv.root[k] = BVH_END;
+  if (use_bvh) {
+    st = ensure_lbvh(s, s->stream);
+    if (st != RTX_OK) return st;
+    for (int k = 0; k < 4; ++k) bv.nodes[k] = s->d_bvh[k], bv.root[k] = s->bvh_root[k];
+  }
   if (n == 0) return RTX_OK;
   DevBuf<double> d_rays, d_t;
   DevBuf<uint32_t> d_id;
@@ -101,7 +111,7 @@ rtx_status rtx_debug_closest_object(rtx_scene* s, uint32_t flags, const double* 
   RTX_CUDA_TRY(s, d_t.alloc(n));
   RTX_CUDA_TRY(s, d_id.alloc(n));
   RTX_CUDA_TRY(s, cudaMemcpyAsync(d_rays.p, rays, n * 48, cudaMemcpyHostToDevice, s->stream));
-  closest_kernel<<<(unsigned)((n + 127) / 128), 128, 0, s->stream>>>(s->d_blob, s->layout, d_rays.p, n, d_t.p, d_id.p);
+  closest_kernel<<<(unsigned)((n + 127) / 128), 128, 0, s->stream>>>(s->d_blob, s->layout, bv, use_bvh ? 1 : 0, d_rays.p, n, d_t.p, d_id.p);
   RTX_CUDA_TRY(s, cudaGetLastError());
   RTX_CUDA_TRY(s, cudaMemcpyAsync(out_t, d_t.p, n * 8, cudaMemcpyDeviceToHost, s->stream));
   RTX_CUDA_TRY(s, cudaMemcpyAsync(out_id, d_id.p, n * 4, cudaMemcpyDeviceToHost, s->stream));

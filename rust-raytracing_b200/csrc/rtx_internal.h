@@ -7,6 +7,7 @@
 #include <vector>
 
 #include "../../include/rtx_cuda.h"
+#include "rtx_lbvh.cuh"
 #include "rtx_render.cuh"
 
 struct rtx_scene {
@@ -20,6 +21,7 @@ struct rtx_scene {
   // host-side packed records (see rtx_scene.cuh); object index = insertion order across all three
   std::vector<double> sph, pl, tri, mat;
   std::vector<uint32_t> sph_id, pl_id, tri_id;
+  std::vector<double> tri_raw;  // 9 doubles per triangle: the LBVH builder needs the vertices for boxes
   uint64_t n_obj = 0;
   bool dirty = true;
 
@@ -27,6 +29,13 @@ struct rtx_scene {
   unsigned char* d_blob = nullptr;
   size_t d_blob_cap = 0;
   rtx::SceneLayout layout{};
+
+  // LBVH: [0] 3-D tree (spheres + triangles), [1..3] prism trees per dropped axis (rtx_lbvh.cuh)
+  rtx::BvhNode* d_bvh[4] = {nullptr, nullptr, nullptr, nullptr};
+  uint32_t bvh_root[4] = {0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu};
+  uint32_t bvh_count[4] = {0, 0, 0, 0};
+  uint32_t bvh_build_launches = 0;
+  bool bvh_valid = false;
 
   // separable sin/cos tables of get_ray_dir, cached per (width, height, fov)
   double* d_tables = nullptr;  // [sin_x W][cos_x W][sin_y H][cos_y H]
@@ -58,6 +67,11 @@ rtx_status ensure_uploaded(rtx_scene* s, cudaStream_t stream);
 // Builds (or reuses) the sin/cos tables for this image size.  Asynchronous on `stream`.
 rtx_status ensure_tables(rtx_scene* s, uint32_t width, uint32_t height, cudaStream_t stream);
 cudaError_t launch_render(const RenderParams& p, int sm_count, cudaStream_t stream, uint32_t* out_launches);
+// Builds the LBVH trees if the object list changed since the last build.  Synchronous.
+rtx_status ensure_lbvh(rtx_scene* s, cudaStream_t stream);
+void free_lbvh(rtx_scene* s);
+// Which structure a render with these flags will use (RTX_ACCEL_BRUTE or RTX_ACCEL_LBVH).
+uint32_t choose_accel(const rtx_scene* s, uint32_t flags);
 }  // namespace rtx
 
 #define RTX_CUDA_TRY(scene, expr)                                      \

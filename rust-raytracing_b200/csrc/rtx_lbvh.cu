@@ -1,0 +1,452 @@
+// rtx_lbvh.cu — GPU LBVH build (K4): AABBs → Morton codes → radix sort → Karras hierarchy → bottom-up refit
+// → escape pointers.  No reference counterpart (the reference scans all objects, scene.rs:243-251); the gate
+// is "hit ids and distances identical to the brute-force kernel".  Everything here is our own kernel code
+// (no CUB/Thrust): the sort is an 8-bit LSD radix sort, one warp per 1024-key tile, stable by construction.
+#include <cuda_runtime.h>
+#include <math_constants.h>
+
+#include <cmath>
+#include <cstring>
+#include <limits>
+#include <vector>
+
+#include "rtx_internal.h"
+#include "rtx_lbvh.cuh"
+
+namespace rtx {
+
+constexpr uint32_t FULLMASK = 0xFFFFFFFFu;
+constexpr int SORT_TILE = 1024;  // keys per warp
+
+__device__ __forceinline__ void atomic_min_f64(double* addr, double v) {
+  unsigned long long* a = reinterpret_cast<unsigned long long*>(addr);
+  unsigned long long old = *a;
+  while (v < __longlong_as_double((long long)old)) {
+    const unsigned long long assumed = old;
+    old = atomicCAS(a, assumed, (unsigned long long)__double_as_longlong(v));
+    if (old == assumed) break;
+  }
+}
+__device__ __forceinline__ void atomic_max_f64(double* addr, double v) {
+  unsigned long long* a = reinterpret_cast<unsigned long long*>(addr);
+  unsigned long long old = *a;
+  while (v > __longlong_as_double((long long)old)) {
+    const unsigned long long assumed = old;
+    old = atomicCAS(a, assumed, (unsigned long long)__double_as_longlong(v));
+    if (old == assumed) break;
+  }
+}
+
+// ---- 1. per-primitive boxes + scene bounds ------------------------------------------------------------------
+// prims[i] = REF_* | index.  open_axis in {0,1,2}: that axis is opened to (-inf,+inf) (prism trees); 3: none.
+// Primitives that can never be hit (non-finite data) get valid = 0: they are left out of the tree.
+// bounds[0..2] = min, [3..5] = max over the finite box corners (used for Morton quantisation and padding).
+__global__ void k_prim_boxes(const double* __restrict__ sph /* cx cy cz r2 */, const double* __restrict__ tri_raw /* 9/tri */,
+                             const uint32_t* __restrict__ prims, uint32_t n, int open_axis, double* __restrict__ lo,
+                             double* __restrict__ hi, uint8_t* __restrict__ valid, double* __restrict__ bounds) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const uint32_t ref = prims[i], idx = ref & REF_INDEX_MASK;
+  double l[3], h[3];
+  if ((ref & ~REF_INDEX_MASK) == REF_SPHERE) {
+    const double* r = sph + (size_t)idx * SPH_STRIDE;
+    const double rad = sqrt(r[3]) * (1.0 + 1e-15);  // >= |radius| (r2 = fl(radius*radius))
+    for (int k = 0; k < 3; ++k) l[k] = r[k] - rad, h[k] = r[k] + rad;
+  } else {
+    const double* v = tri_raw + (size_t)idx * 9;
+    for (int k = 0; k < 3; ++k) {
+      l[k] = fmin(v[k], fmin(v[3 + k], v[6 + k]));
+      h[k] = fmax(v[k], fmax(v[3 + k], v[6 + k]));
+      if (!(v[k] == v[k]) || !(v[3 + k] == v[3 + k]) || !(v[6 + k] == v[6 + k])) l[k] = CUDART_NAN;
+    }
+  }
+  bool ok = true;
+  for (int k = 0; k < 3; ++k) ok = ok && (l[k] - l[k] == 0.0) && (h[k] - h[k] == 0.0);  // finite
+  valid[i] = ok ? 1 : 0;
+  if (!ok) {
+    for (int k = 0; k < 3; ++k) l[k] = CUDART_INF, h[k] = -CUDART_INF;
+  } else {
+    for (int k = 0; k < 3; ++k) {
+      atomic_min_f64(&bounds[k], l[k]);
+      atomic_max_f64(&bounds[3 + k], h[k]);
+    }
+    if (open_axis < 3) l[open_axis] = -CUDART_INF, h[open_axis] = CUDART_INF;
+  }
+  for (int k = 0; k < 3; ++k) lo[(size_t)i * 3 + k] = l[k], hi[(size_t)i * 3 + k] = h[k];
+}
+
+// ---- 2. Morton keys -----------------------------------------------------------------------------------------
+__device__ __forceinline__ uint64_t spread3(uint64_t x) {  // 21 bits → every third bit
+  x &= 0x1fffffULL;
+  x = (x | x << 32) & 0x1f00000000ffffULL;
+  x = (x | x << 16) & 0x1f0000ff0000ffULL;
+  x = (x | x << 8) & 0x100f00f00f00f00fULL;
+  x = (x | x << 4) & 0x10c30c30c30c30c3ULL;
+  x = (x | x << 2) & 0x1249249249249249ULL;
+  return x;
+}
+// 63-bit code of the box centre inside `bounds`; an opened axis contributes 0; invalid prims sort last.
+__global__ void k_morton(const double* __restrict__ lo, const double* __restrict__ hi, const uint8_t* __restrict__ valid,
+                         uint32_t n, int open_axis, const double* __restrict__ bounds, uint64_t* __restrict__ keys,
+                         uint32_t* __restrict__ vals) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  vals[i] = i;
+  if (!valid[i]) {
+    keys[i] = ~0ULL;
+    return;
+  }
+  uint64_t q[3];
+  for (int k = 0; k < 3; ++k) {
+    if (k == open_axis) {
+      q[k] = 0;
+      continue;
+    }
+    const double ext = bounds[3 + k] - bounds[k];
+    const double c = 0.5 * lo[(size_t)i * 3 + k] + 0.5 * hi[(size_t)i * 3 + k];
+    double u = ext > 0.0 ? (c - bounds[k]) / ext : 0.0;
+    u = fmin(fmax(u, 0.0), 1.0);
+    q[k] = (uint64_t)fmin(u * 2097152.0, 2097151.0);
+  }
+  keys[i] = (spread3(q[0]) << 2) | (spread3(q[1]) << 1) | spread3(q[2]);
+}
+
+// ---- 3. LSD radix sort, 8 bits per pass, one warp per SORT_TILE keys ------------------------------------------
+__global__ void k_sort_hist(const uint64_t* __restrict__ keys, uint32_t n, int shift, uint32_t ntiles,
+                            uint32_t* __restrict__ hist /* [256][ntiles] */) {
+  __shared__ uint32_t cnt[8][256];
+  const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t tile = blockIdx.x * 8 + warp;
+  for (int d = lane; d < 256; d += 32) cnt[warp][d] = 0;
+  __syncwarp();
+  if (tile < ntiles) {
+    const uint32_t base = tile * SORT_TILE;
+    for (int c = 0; c < SORT_TILE; c += 32) {
+      const uint32_t i = base + c + lane;
+      if (i < n) atomicAdd(&cnt[warp][(keys[i] >> shift) & 255], 1u);
+    }
+    __syncwarp();
+    for (int d = lane; d < 256; d += 32) hist[(size_t)d * ntiles + tile] = cnt[warp][d];
+  }
+}
+// exclusive scan of hist (digit-major, then tile) in place; single block
+__global__ void k_sort_scan(uint32_t* __restrict__ hist, uint32_t total) {
+  __shared__ uint32_t warp_sums[32];
+  __shared__ uint32_t carry;
+  if (threadIdx.x == 0) carry = 0;
+  __syncthreads();
+  const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  for (uint32_t base = 0; base < total; base += blockDim.x) {
+    const uint32_t i = base + threadIdx.x;
+    const uint32_t v = i < total ? hist[i] : 0;
+    uint32_t x = v;
+    for (int o = 1; o < 32; o <<= 1) {
+      const uint32_t y = __shfl_up_sync(FULLMASK, x, o);
+      if (lane >= o) x += y;
+    }
+    if (lane == 31) warp_sums[warp] = x;
+    __syncthreads();
+    if (warp == 0) {
+      uint32_t s = lane < (blockDim.x >> 5) ? warp_sums[lane] : 0;
+      for (int o = 1; o < 32; o <<= 1) {
+        const uint32_t y = __shfl_up_sync(FULLMASK, s, o);
+        if (lane >= o) s += y;
+      }
+      warp_sums[lane] = s;  // inclusive
+    }
+    __syncthreads();
+    const uint32_t before = (warp ? warp_sums[warp - 1] : 0) + carry;
+    if (i < total) hist[i] = before + x - v;
+    __syncthreads();
+    if (threadIdx.x == blockDim.x - 1) carry = before + x;
+    __syncthreads();
+  }
+}
+__global__ void k_sort_scatter(const uint64_t* __restrict__ keys, const uint32_t* __restrict__ vals, uint32_t n, int shift,
+                               uint32_t ntiles, const uint32_t* __restrict__ hist, uint64_t* __restrict__ keys_out,
+                               uint32_t* __restrict__ vals_out) {
+  __shared__ uint32_t off[8][256];
+  const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t tile = blockIdx.x * 8 + warp;
+  if (tile >= ntiles) return;
+  for (int d = lane; d < 256; d += 32) off[warp][d] = hist[(size_t)d * ntiles + tile];
+  __syncwarp();
+  const uint32_t base = tile * SORT_TILE;
+  for (int c = 0; c < SORT_TILE; c += 32) {
+    const uint32_t i = base + c + lane;
+    const bool act = i < n;
+    const uint32_t active = __ballot_sync(FULLMASK, act);
+    if (act) {
+      const uint64_t k = keys[i];
+      const uint32_t d = (uint32_t)(k >> shift) & 255u;
+      const uint32_t peers = __match_any_sync(active, d);
+      const uint32_t rank = __popc(peers & ((1u << lane) - 1u));
+      const uint32_t dst = off[warp][d] + rank;  // all peers read before the leader bumps it
+      __syncwarp(active);
+      if (rank == 0) off[warp][d] += __popc(peers);
+      keys_out[dst] = k;
+      vals_out[dst] = vals[i];
+    }
+    __syncwarp();
+  }
+}
+
+// ---- 4. Karras 2012 hierarchy over the m sorted valid keys ---------------------------------------------------
+// Node numbering: internal nodes 0..m-2 (root = 0), leaf j = node (m-1) + j.  m == 1: the single leaf is root.
+__device__ __forceinline__ int delta(const uint64_t* __restrict__ keys, int m, int i, int j) {
+  if (j < 0 || j >= m) return -1;
+  const uint64_t a = keys[i], b = keys[j];
+  if (a == b) return 64 + __clz(i ^ j);  // duplicate codes: fall back to the index
+  return __clzll((long long)(a ^ b));
+}
+__global__ void k_hierarchy(const uint64_t* __restrict__ keys, int m, uint32_t* __restrict__ left,
+                            uint32_t* __restrict__ right, uint32_t* __restrict__ parent) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= m - 1) return;
+  const int d = (delta(keys, m, i, i + 1) - delta(keys, m, i, i - 1)) >= 0 ? 1 : -1;
+  const int dmin = delta(keys, m, i, i - d);
+  int lmax = 2;
+  while (delta(keys, m, i, i + lmax * d) > dmin) lmax <<= 1;
+  int l = 0;
+  for (int t = lmax >> 1; t >= 1; t >>= 1)
+    if (delta(keys, m, i, i + (l + t) * d) > dmin) l += t;
+  const int j = i + l * d;
+  const int dnode = delta(keys, m, i, j);
+  int s = 0, t = l;
+  do {
+    t = (t + 1) >> 1;
+    if (delta(keys, m, i, i + (s + t) * d) > dnode) s += t;
+  } while (t > 1);
+  const int gamma = i + s * d + min(d, 0);
+  const uint32_t lc = (min(i, j) == gamma) ? (uint32_t)(m - 1 + gamma) : (uint32_t)gamma;
+  const uint32_t rc = (max(i, j) == gamma + 1) ? (uint32_t)(m - 1 + gamma + 1) : (uint32_t)(gamma + 1);
+  left[i] = lc;
+  right[i] = rc;
+  parent[lc] = (uint32_t)i;
+  parent[rc] = (uint32_t)i;
+  if (i == 0) parent[0] = BVH_END;
+}
+
+// ---- 5. leaves + bottom-up refit (second arrival at a node merges its children) --------------------------------
+__global__ void k_refit(const uint32_t* __restrict__ sorted_vals, const uint32_t* __restrict__ prims,
+                        const double* __restrict__ lo, const double* __restrict__ hi, int m, double pad,
+                        const uint32_t* __restrict__ left, const uint32_t* __restrict__ right,
+                        const uint32_t* __restrict__ parent, uint32_t* __restrict__ flags, BvhNode* __restrict__ nodes) {
+  const int j = blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= m) return;
+  const uint32_t src = sorted_vals[j];
+  const uint32_t self = (uint32_t)(m - 1 + j);
+  BvhNode nd;
+  for (int k = 0; k < 3; ++k) {
+    nd.lo[k] = lo[(size_t)src * 3 + k] - pad;  // -inf - pad = -inf for opened axes
+    nd.hi[k] = hi[(size_t)src * 3 + k] + pad;
+  }
+  nd.left = BVH_END;
+  nd.escape = BVH_END;
+  nd.prim = prims[src];
+  nd.pad = 0;
+  nodes[self] = nd;
+  if (m == 1) return;
+  __threadfence();
+  uint32_t cur = parent[self];
+  while (cur != BVH_END) {
+    if (atomicAdd(&flags[cur], 1u) == 0u) return;  // first arrival: the sibling subtree is not ready
+    __threadfence();
+    const volatile BvhNode* a = nodes + left[cur];
+    const volatile BvhNode* b = nodes + right[cur];
+    BvhNode p;
+    for (int k = 0; k < 3; ++k) {
+      p.lo[k] = fmin(a->lo[k], b->lo[k]);
+      p.hi[k] = fmax(a->hi[k], b->hi[k]);
+    }
+    p.left = left[cur];
+    p.escape = BVH_END;
+    p.prim = BVH_NO_PRIM;
+    p.pad = 0;
+    nodes[cur] = p;
+    __threadfence();
+    cur = parent[cur];
+  }
+}
+
+// ---- 6. escape pointers: next node in depth-first order once a subtree is finished ----------------------------
+__global__ void k_escape(int total_nodes, const uint32_t* __restrict__ right, const uint32_t* __restrict__ parent,
+                         BvhNode* __restrict__ nodes) {
+  const int x = blockIdx.x * blockDim.x + threadIdx.x;
+  if (x >= total_nodes) return;
+  uint32_t c = (uint32_t)x;
+  uint32_t esc = BVH_END;
+  for (;;) {
+    const uint32_t p = parent[c];
+    if (p == BVH_END) break;
+    if (right[p] != c) {  // c is a left child: continue with its sibling
+      esc = right[p];
+      break;
+    }
+    c = p;
+  }
+  nodes[x].escape = esc;
+}
+
+__global__ void k_count_valid(const uint64_t* __restrict__ sorted_keys, uint32_t n, uint32_t* __restrict__ out) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  // keys are sorted: the first invalid key marks m
+  if (sorted_keys[i] == ~0ULL && (i == 0 || sorted_keys[i - 1] != ~0ULL)) *out = i;
+}
+
+// ---- host orchestration ---------------------------------------------------------------------------------------
+template <typename T>
+struct Tmp {
+  T* p = nullptr;
+  ~Tmp() {
+    if (p) cudaFree(p);
+  }
+  cudaError_t alloc(size_t n) { return cudaMalloc((void**)&p, (n ? n : 1) * sizeof(T)); }
+};
+
+#define LBVH_TRY(expr)                                          \
+  do {                                                          \
+    cudaError_t _e = (expr);                                    \
+    if (_e != cudaSuccess) return cuda_fail(s, _e, #expr);      \
+  } while (0)
+
+// Builds one tree over `prims` (host list of REF_*|index).  Synchronous on `stream`.
+static rtx_status build_tree(rtx_scene* s, const std::vector<uint32_t>& prims, int open_axis, const double* d_tri_raw,
+                             cudaStream_t stream, BvhNode** out_nodes, uint32_t* out_root, uint32_t* out_count,
+                             uint32_t* launches) {
+  *out_nodes = nullptr;
+  *out_root = BVH_END;
+  *out_count = 0;
+  const uint32_t n = (uint32_t)prims.size();
+  if (n == 0) return RTX_OK;
+  const unsigned B = 256, G = (n + B - 1) / B;
+  Tmp<uint32_t> d_prims, d_vals[2], d_hist, d_left, d_right, d_parent, d_flags, d_m;
+  Tmp<double> d_lo, d_hi, d_bounds;
+  Tmp<uint8_t> d_valid;
+  Tmp<uint64_t> d_keys[2];
+  LBVH_TRY(d_prims.alloc(n));
+  LBVH_TRY(d_lo.alloc((size_t)n * 3));
+  LBVH_TRY(d_hi.alloc((size_t)n * 3));
+  LBVH_TRY(d_valid.alloc(n));
+  LBVH_TRY(d_bounds.alloc(6));
+  LBVH_TRY(d_keys[0].alloc(n));
+  LBVH_TRY(d_keys[1].alloc(n));
+  LBVH_TRY(d_vals[0].alloc(n));
+  LBVH_TRY(d_vals[1].alloc(n));
+  LBVH_TRY(d_m.alloc(1));
+  LBVH_TRY(cudaMemcpyAsync(d_prims.p, prims.data(), (size_t)n * 4, cudaMemcpyHostToDevice, stream));
+  const double inf = std::numeric_limits<double>::infinity();
+  const double b0[6] = {inf, inf, inf, -inf, -inf, -inf};
+  LBVH_TRY(cudaMemcpyAsync(d_bounds.p, b0, sizeof(b0), cudaMemcpyHostToDevice, stream));
+  const double* d_sph = reinterpret_cast<const double*>(s->d_blob + s->layout.off_sph);
+  k_prim_boxes<<<G, B, 0, stream>>>(d_sph, d_tri_raw, d_prims.p, n, open_axis, d_lo.p, d_hi.p, d_valid.p, d_bounds.p);
+  k_morton<<<G, B, 0, stream>>>(d_lo.p, d_hi.p, d_valid.p, n, open_axis, d_bounds.p, d_keys[0].p, d_vals[0].p);
+  *launches += 2;
+  // radix sort: 8 passes x 8 bits
+  const uint32_t ntiles = (n + SORT_TILE - 1) / SORT_TILE;
+  LBVH_TRY(d_hist.alloc((size_t)256 * ntiles));
+  int cur = 0;
+  for (int pass = 0; pass < 8; ++pass) {
+    const unsigned gb = (ntiles + 7) / 8;
+    k_sort_hist<<<gb, 256, 0, stream>>>(d_keys[cur].p, n, pass * 8, ntiles, d_hist.p);
+    k_sort_scan<<<1, 1024, 0, stream>>>(d_hist.p, 256u * ntiles);
+    k_sort_scatter<<<gb, 256, 0, stream>>>(d_keys[cur].p, d_vals[cur].p, n, pass * 8, ntiles, d_hist.p, d_keys[cur ^ 1].p,
+                                           d_vals[cur ^ 1].p);
+    cur ^= 1;
+    *launches += 3;
+  }
+  // m = number of valid primitives (invalid keys = ~0 sorted last)
+  LBVH_TRY(cudaMemcpyAsync(d_m.p, &n, 4, cudaMemcpyHostToDevice, stream));
+  k_count_valid<<<G, B, 0, stream>>>(d_keys[cur].p, n, d_m.p);
+  *launches += 1;
+  uint32_t m = 0;
+  double hb[6];
+  LBVH_TRY(cudaMemcpyAsync(&m, d_m.p, 4, cudaMemcpyDeviceToHost, stream));
+  LBVH_TRY(cudaMemcpyAsync(hb, d_bounds.p, sizeof(hb), cudaMemcpyDeviceToHost, stream));
+  LBVH_TRY(cudaStreamSynchronize(stream));
+  if (m == 0) return RTX_OK;
+  double scale = 1e-300;
+  for (int k = 0; k < 6; ++k) scale = std::fmax(scale, std::fabs(hb[k]));
+  const double pad = scale * 9.5367431640625e-07;  // 2^-20 x scene scale (see rtx_lbvh.cuh)
+  const uint32_t total = 2 * m - 1;
+  BvhNode* nodes = nullptr;
+  LBVH_TRY(cudaMalloc((void**)&nodes, (size_t)total * sizeof(BvhNode)));
+  rtx_status st = RTX_OK;
+  do {
+    cudaError_t e;
+    if ((e = d_left.alloc(m)) != cudaSuccess || (e = d_right.alloc(m)) != cudaSuccess ||
+        (e = d_parent.alloc(total)) != cudaSuccess || (e = d_flags.alloc(m)) != cudaSuccess ||
+        (e = cudaMemsetAsync(d_flags.p, 0, (size_t)m * 4, stream)) != cudaSuccess ||
+        (e = cudaMemsetAsync(d_parent.p, 0xFF, (size_t)total * 4, stream)) != cudaSuccess) {
+      st = cuda_fail(s, e, "lbvh temporaries");
+      break;
+    }
+    const unsigned Gm = (m + B - 1) / B, Gt = (total + B - 1) / B;
+    if (m > 1) k_hierarchy<<<Gm, B, 0, stream>>>(d_keys[cur].p, (int)m, d_left.p, d_right.p, d_parent.p);
+    k_refit<<<Gm, B, 0, stream>>>(d_vals[cur].p, d_prims.p, d_lo.p, d_hi.p, (int)m, pad, d_left.p, d_right.p, d_parent.p,
+                                  d_flags.p, nodes);
+    if (m > 1) k_escape<<<Gt, B, 0, stream>>>((int)total, d_right.p, d_parent.p, nodes);
+    *launches += 3;
+    if ((e = cudaGetLastError()) != cudaSuccess || (e = cudaStreamSynchronize(stream)) != cudaSuccess) {
+      st = cuda_fail(s, e, "lbvh build kernels");
+      break;
+    }
+  } while (0);
+  if (st != RTX_OK) {
+    cudaFree(nodes);
+    return st;
+  }
+  *out_nodes = nodes;
+  *out_root = (m == 1) ? 0u : 0u;  // internal root = node 0; with m == 1 the only node (the leaf) is node 0 too
+  *out_count = total;
+  return RTX_OK;
+}
+
+void free_lbvh(rtx_scene* s) {
+  for (int k = 0; k < 4; ++k) {
+    if (s->d_bvh[k]) cudaFree(s->d_bvh[k]);
+    s->d_bvh[k] = nullptr;
+    s->bvh_root[k] = BVH_END;
+    s->bvh_count[k] = 0;
+  }
+  s->bvh_valid = false;
+}
+
+// Builds the 3-D tree (spheres + triangles) and one prism tree per dropped axis (triangles).  The scene blob
+// must be uploaded.  Rebuilt whenever the object list changed.
+rtx_status ensure_lbvh(rtx_scene* s, cudaStream_t stream) {
+  if (s->bvh_valid) return RTX_OK;
+  free_lbvh(s);
+  const uint32_t n_sph = (uint32_t)s->sph_id.size(), n_tri = (uint32_t)s->tri_id.size();
+  std::vector<uint32_t> all, prism[3];
+  all.reserve((size_t)n_sph + n_tri);
+  for (uint32_t i = 0; i < n_sph; ++i) all.push_back(REF_SPHERE | i);
+  for (uint32_t i = 0; i < n_tri; ++i) {
+    uint64_t code;
+    std::memcpy(&code, &s->tri[(size_t)i * TRI_STRIDE + 13], 8);
+    if (code & (TRI_DEGENERATE | TRI_PANIC)) continue;  // contains() is never true: cannot be hit
+    all.push_back(REF_TRIANGLE | i);
+    const int i1 = (int)((code >> TRI_I1_SHIFT) & 3), i2 = (int)((code >> TRI_I2_SHIFT) & 3);
+    prism[3 - i1 - i2].push_back(REF_TRIANGLE | i);  // the coordinate contains() never looks at
+  }
+  Tmp<double> d_tri_raw;
+  if (n_tri) {
+    LBVH_TRY(d_tri_raw.alloc(s->tri_raw.size()));
+    LBVH_TRY(cudaMemcpyAsync(d_tri_raw.p, s->tri_raw.data(), s->tri_raw.size() * 8, cudaMemcpyHostToDevice, stream));
+  }
+  uint32_t launches = 0;
+  rtx_status st = build_tree(s, all, 3, d_tri_raw.p, stream, &s->d_bvh[0], &s->bvh_root[0], &s->bvh_count[0], &launches);
+  for (int a = 0; a < 3 && st == RTX_OK; ++a)
+    st = build_tree(s, prism[a], a, d_tri_raw.p, stream, &s->d_bvh[1 + a], &s->bvh_root[1 + a], &s->bvh_count[1 + a],
+                    &launches);
+  if (st != RTX_OK) {
+    free_lbvh(s);
+    return st;
+  }
+  s->bvh_build_launches = launches;
+  s->bvh_valid = true;
+  return RTX_OK;
+}
+
+}  // namespace rtx

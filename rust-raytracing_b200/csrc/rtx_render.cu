@@ -18,6 +18,7 @@
 #include <cuda_runtime.h>
 #include <math_constants.h>
 
+#include "rtx_lbvh.cuh"
 #include "rtx_render.cuh"
 #include "rtx_trace.cuh"
 
@@ -59,7 +60,7 @@ __device__ __forceinline__ void stage_blob(unsigned char* dst, const unsigned ch
       : "memory");
 }
 
-template <bool SMEM_SCENE>
+template <bool SMEM_SCENE, bool USE_BVH>
 __global__ void __launch_bounds__(RENDER_BLOCK, 2) render_megakernel(const __grid_constant__ RenderParams p) {
   extern __shared__ __align__(128) unsigned char smem_raw[];
   const unsigned char* base = p.scene_blob;
@@ -100,6 +101,8 @@ __global__ void __launch_bounds__(RENDER_BLOCK, 2) render_megakernel(const __gri
   rng.s = 0;
   // counters
   uint32_t n_rays = 0, n_paths = 0, n_panics = 0, n_hits = 0;
+  TraversalCounters tc;
+  tc.nodes = 0, tc.prims = 0;
 
   for (;;) {
     // ---- 1. pixel acquisition: lanes without a pixel take the next slots of the warp's granule ----
@@ -178,7 +181,7 @@ __global__ void __launch_bounds__(RENDER_BLOCK, 2) render_megakernel(const __gri
       if (sc.n_obj == 0) {
         end = true;  // scene.rs:224-226
       } else {
-        const Hit h = closest_brute(sc, pos, dir, &n_panics);
+        const Hit h = USE_BVH ? closest_lbvh(sc, p.bvh, pos, dir, &n_panics, tc) : closest_brute(sc, pos, dir, &n_panics);
         ++n_rays;
         if (segment == 0 && sample == 0 && p.out_ids) p.out_ids[out_index] = h.id;
         if (h.id == MISS_ID) {
@@ -225,17 +228,22 @@ __global__ void __launch_bounds__(RENDER_BLOCK, 2) render_megakernel(const __gri
   // ---- counters: one atomic per warp ----
   if (p.ray_counter) {
     unsigned long long r = n_rays, q = n_paths, e = n_panics, hh = n_hits;
+    unsigned long long nv = tc.nodes, pt = USE_BVH ? (unsigned long long)tc.prims : (unsigned long long)n_rays * sc.n_obj;
     for (int o = 16; o > 0; o >>= 1) {
       r += __shfl_down_sync(FULL, r, o);
       q += __shfl_down_sync(FULL, q, o);
       e += __shfl_down_sync(FULL, e, o);
       hh += __shfl_down_sync(FULL, hh, o);
+      nv += __shfl_down_sync(FULL, nv, o);
+      pt += __shfl_down_sync(FULL, pt, o);
     }
     if (lane == 0) {
       atomicAdd(&p.ray_counter[0], r);
       atomicAdd(&p.ray_counter[1], q);
       if (e) atomicAdd(&p.ray_counter[2], e);
       atomicAdd(&p.ray_counter[3], hh);
+      if (nv) atomicAdd(&p.ray_counter[4], nv);
+      atomicAdd(&p.ray_counter[5], pt);
     }
   }
 }
@@ -253,13 +261,19 @@ cudaError_t launch_render(const RenderParams& p, int sm_count, cudaStream_t stre
   uint64_t want_blocks = (total_work + (RENDER_BLOCK / 32) - 1) / (RENDER_BLOCK / 32);
   uint64_t grid = (uint64_t)sm_count * blocks_per_sm;
   if (want_blocks < grid) grid = want_blocks ? want_blocks : 1;
-  if (use_smem) {
-    e = cudaFuncSetAttribute(render_megakernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    if (e != cudaSuccess) return e;
-    render_megakernel<true><<<(unsigned)grid, RENDER_BLOCK, smem, stream>>>(p);
-  } else {
-    render_megakernel<false><<<(unsigned)grid, RENDER_BLOCK, 0, stream>>>(p);
-  }
+  auto launch = [&](auto kernel) -> cudaError_t {
+    if (smem) {
+      cudaError_t a = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+      if (a != cudaSuccess) return a;
+    }
+    kernel<<<(unsigned)grid, RENDER_BLOCK, smem, stream>>>(p);
+    return cudaSuccess;
+  };
+  if (use_smem)
+    e = p.use_bvh ? launch(render_megakernel<true, true>) : launch(render_megakernel<true, false>);
+  else
+    e = p.use_bvh ? launch(render_megakernel<false, true>) : launch(render_megakernel<false, false>);
+  if (e != cudaSuccess) return e;
   if (out_launches) *out_launches += 1;
   return cudaGetLastError();
 }

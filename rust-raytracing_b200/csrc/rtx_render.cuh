@@ -1,5 +1,6 @@
 // rtx_render.cuh — launch parameters shared between the API layer and the render kernels.
 #pragma once
+#include "rtx_lbvh.cuh"
 #include "rtx_scene.cuh"
 
 namespace rtx {
@@ -29,6 +30,8 @@ struct RenderParams {
   // scene
   const unsigned char* scene_blob;
   SceneLayout layout;
+  BvhView bvh;       // used when use_bvh != 0
+  uint32_t use_bvh;
   // image shard
   uint32_t shard_index, shard_count;
   uint32_t tiles_x, tiles_y;
@@ -38,7 +41,7 @@ struct RenderParams {
   // outputs
   double* out_rgb;                  // may be null (RTX_FLAG_NO_RADIANCE)
   uint32_t* out_ids;                // may be null
-  unsigned long long* ray_counter;  // [0] rays, [1] paths, [2] triangle panics, [3] hits; may be null
+  unsigned long long* ray_counter;  // [0] rays, [1] paths, [2] triangle panics, [3] hits, [4] nodes visited, [5] prims tested; may be null
 };
 
 }  // namespace rtx

@@ -73,7 +73,7 @@ def render_distributed(scene, width, height, seed, group=None, flags=RTX_ACCEL_A
     uint64[4] {rays, paths, triangle_panics, hits} device tensor."""
     world, rank = dist.get_world_size(group), dist.get_rank(group)
     dev = torch.device("cuda", scene.device)
-    counters = torch.zeros(4, dtype=torch.int64, device=dev)
+    counters = torch.zeros(8, dtype=torch.int64, device=dev)
     if world == 1:
         rgb = torch.empty((height, width, 3), dtype=torch.float64, device=dev)
         ids = torch.empty((height, width), dtype=torch.int32, device=dev) if want_ids else None
@@ -98,7 +98,7 @@ def render_all_shards_on_one_gpu(scene, width, height, seed, world, flags=RTX_AC
     slots = shard_slots(width, height, world)
     g_rgb = torch.zeros((world, slots, RTX_TILE, RTX_TILE, 3), dtype=torch.float64, device=dev)
     g_ids = torch.full((world, slots, RTX_TILE, RTX_TILE), -1, dtype=torch.int32, device=dev)
-    counters = torch.zeros(4, dtype=torch.int64, device=dev)
+    counters = torch.zeros(8, dtype=torch.int64, device=dev)
     for r in range(world):
         render_shard(scene, width, height, seed, r, world, g_rgb[r], g_ids[r], counters, flags)
     rgb, ids = deinterleave(width, height, world, g_rgb, g_ids)

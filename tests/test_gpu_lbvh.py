@@ -1,0 +1,172 @@
+"""GPU: the LBVH (K4 build + K5 stackless traversal) must return exactly what the O(N) scan of
+scene.rs:243-251 returns — same distance bits, same object index (lowest index on ties), including the
+reference's phantom triangle hits.  Gate: LBVH == brute-force kernel, bit for bit; brute force itself is
+gated against the oracle in test_gpu_functions.py / test_gpu_render.py."""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+
+def _rays(rng, n, spread):
+    pos = rng.uniform(-spread, spread, (n, 3))
+    d = rng.normal(size=(n, 3))
+    d /= np.linalg.norm(d, axis=1, keepdims=True)
+    return np.concatenate([pos, d], axis=1)
+
+
+def _same(sc, rtx, rays):
+    tb, ib = sc.debug_closest_object(rays, flags=rtx.RTX_ACCEL_BRUTE)
+    tl, il = sc.debug_closest_object(rays, flags=rtx.RTX_ACCEL_LBVH)
+    assert np.array_equal(ib, il), f"{(ib != il).sum()} of {len(ib)} hit ids differ"
+    assert tb.tobytes() == tl.tobytes()
+    return ib
+
+
+def _visible_triangles(rng, n, spread=20.0, size=2.0):
+    out = []
+    while len(out) < n:
+        c = rng.uniform(-spread, spread, 3)
+        v = c + rng.uniform(-size, size, (3, 3))
+        nrm = np.cross(v[1] - v[0], v[2] - v[0])
+        ln = np.linalg.norm(nrm)
+        if ln < 1e-3:
+            continue
+        if (nrm / ln) @ v[0] < 0:
+            v = v[[0, 2, 1]]
+        out.append(v.ravel())
+    return np.array(out)
+
+
+def _mats(n):
+    return np.tile([0.6, 0.6, 0.6, 0, 0, 0, 1.0], (n, 1))
+
+
+def test_spheres_lbvh_equals_scan(rtx, gpu):
+    rng = np.random.default_rng(21)
+    n = 3000
+    sc = rtx.Scene(rtx.Config(), rtx.Camera((0, 0, 0), (1, 0, 0), 1.0))
+    centers = rng.uniform(-30, 30, (n, 3))
+    radii = rng.uniform(0.05, 2.0, n)
+    centers[100:110] = centers[0:10]  # exact duplicates → distance ties → lowest index must win
+    radii[100:110] = radii[0:10]
+    sc.add_spheres(centers, radii, _mats(n))
+    rays = _rays(rng, 60000, 35.0)
+    # rays starting exactly on surfaces and at centres
+    k = 2000
+    nrm = rng.normal(size=(k, 3))
+    nrm /= np.linalg.norm(nrm, axis=1, keepdims=True)
+    rays[:k, :3] = centers[:k] + nrm * radii[:k, None]
+    rays[k:k + 500, :3] = centers[:500]
+    ids = _same(sc, rtx, rays)
+    assert (ids != rtx.MISS_ID).mean() > 0.3
+    dup = set(range(100, 110))
+    assert not (dup & set(ids.tolist()))  # the higher-index duplicate never wins
+
+
+def test_triangles_lbvh_equals_scan_including_phantoms(rtx, oracle, gpu):
+    rng = np.random.default_rng(22)
+    tris = _visible_triangles(rng, 1500)
+    # other pivot classes: r.x == 0 (dropped axis differs) and vertical walls
+    special = np.array([
+        [0, 0, -25, 0, 4, -25, 4, 0, -25.0],
+        [25, 0, 0, 25, 0, 4, 25, -4, 0.0],
+        [2, 0, 13, 4, 0, 13, 2, 0, 17.0],
+        [0, 0, 5, 0, 0, 5, 0, 4, 5.0],       # degenerate
+    ])
+    tris = np.concatenate([tris, special])
+    sc = rtx.Scene(rtx.Config(), rtx.Camera((0, 0, 0), (1, 0, 0), 1.0))
+    sc.add_triangles(tris, _mats(len(tris)))
+    rays = _rays(rng, 60000, 25.0)
+    # bounce-like rays: origins ON triangles (self-hit noise |t| ~ 1e-16 must match bit for bit)
+    k = 20000
+    t = tris[rng.integers(0, 1500, k)].reshape(k, 3, 3)
+    a = rng.uniform(0, 1, (k, 1))
+    b = rng.uniform(0, 1, (k, 1)) * (1 - a)
+    rays[:k, :3] = t[:, 0] + a * (t[:, 1] - t[:, 0]) + b * (t[:, 2] - t[:, 0])
+    ids = _same(sc, rtx, rays)
+    assert (ids != rtx.MISS_ID).mean() > 0.3
+    # and the scan agrees with the oracle on a subset (ties the LBVH to the reference semantics)
+    objs = oracle.make_objects(*sc.objects_flat())
+    t_ref, i_ref = oracle.closest_object(objs, rays[:3000])
+    t_l, i_l = sc.debug_closest_object(rays[:3000], flags=rtx.RTX_ACCEL_LBVH)
+    assert np.array_equal(i_ref, i_l) and t_ref.tobytes() == t_l.tobytes()
+    # a pure phantom configuration: everything is behind the rays
+    ph = _rays(rng, 20000, 10.0)
+    ph[:, 2] = 60.0
+    ph[:, 5] = np.abs(ph[:, 5])
+    ids = _same(sc, rtx, ph)
+    assert (ids != rtx.MISS_ID).any()  # phantom hits exist and the prism trees find them
+
+
+def test_mixed_scene_with_planes_and_invalid_prims(rtx, gpu):
+    rng = np.random.default_rng(23)
+    sc = rtx.Scene(rtx.Config(), rtx.Camera((0, 0, 0), (1, 0, 0), 1.0))
+    sc.add_planes([[0, 0, -12]], [[0, 0, 1]], _mats(1))
+    sc.add_spheres(rng.uniform(-10, 10, (200, 3)), rng.uniform(0.1, 1.5, 200), _mats(200))
+    sc.add_triangles(_visible_triangles(rng, 200, spread=10.0), _mats(200))
+    sc.add_spheres([[np.nan, 0, 0], [0, 0, 0], [1, 2, 3]], [1.0, np.inf, np.nan], _mats(3))  # can never be hit
+    sc.add_planes([[0, 0, 14]], [[0, 0, -1]], _mats(1))
+    sc.add_spheres(rng.uniform(-10, 10, (100, 3)), rng.uniform(0.1, 1.5, 100), _mats(100))
+    ids = _same(sc, rtx, _rays(rng, 50000, 11.0))
+    seen = set(ids.tolist())
+    assert 0 in seen and 404 in seen and not ({401, 402, 403} & seen)
+
+
+def test_tiny_trees(rtx, gpu):
+    rng = np.random.default_rng(24)
+    for n in (1, 2, 3):
+        sc = rtx.Scene(rtx.Config(), rtx.Camera((0, 0, 0), (1, 0, 0), 1.0))
+        sc.add_spheres(rng.uniform(-3, 3, (n, 3)), rng.uniform(0.5, 1.5, n), _mats(n))
+        _same(sc, rtx, _rays(rng, 5000, 5.0))
+    sc = rtx.Scene(rtx.Config(), rtx.Camera((0, 0, 0), (1, 0, 0), 1.0))
+    sc.add_triangles(_visible_triangles(rng, 1, spread=3.0), _mats(1))
+    _same(sc, rtx, _rays(rng, 5000, 5.0))
+
+
+@pytest.mark.parametrize("which", ["spheres", "terrain"])
+def test_whole_image_lbvh_equals_scan(rtx, gpu, which):
+    from rtx_b200 import scenes
+    if which == "spheres":
+        sc, (w, h) = scenes.random_spheres(n=2000, rays_per_pixel=2, max_bounces=8), (320, 180)
+    else:
+        sc, (w, h) = scenes.terrain(grid=64, rays_per_pixel=2, max_bounces=4), (256, 144)
+    a, ia = sc.render(w, h, seed=1, flags=rtx.RTX_ACCEL_BRUTE, want_ids=True)
+    sa = (sc.last_stats.rays, sc.last_stats.hits, sc.last_stats.accel_used)
+    b, ib = sc.render(w, h, seed=1, flags=rtx.RTX_ACCEL_LBVH, want_ids=True)
+    sb = (sc.last_stats.rays, sc.last_stats.hits, sc.last_stats.accel_used)
+    assert a.tobytes() == b.tobytes() and np.array_equal(ia, ib)
+    assert sa[:2] == sb[:2] and sa[2] == rtx.RTX_ACCEL_BRUTE and sb[2] == rtx.RTX_ACCEL_LBVH
+    st = sc.last_stats
+    assert st.nodes_visited > 0 and st.prims_tested < st.rays * sc.object_count / 10
+    print(f"{which}: {st.rays} rays, {st.nodes_visited / st.rays:.1f} nodes/ray, {st.prims_tested / st.rays:.1f} prims/ray")
+    c = sc.render(w, h, seed=1)  # AUTO picks the LBVH here
+    assert sc.last_stats.accel_used == rtx.RTX_ACCEL_LBVH and c.tobytes() == b.tobytes()
+
+
+def test_s2_10k_spheres_against_oracle(rtx, oracle, gpu):
+    """Config C3's scene at a size the oracle's O(N) scan finishes in seconds."""
+    from rtx_b200 import scenes
+    sc = scenes.random_spheres(n=10_000, rays_per_pixel=1, max_bounces=8)
+    w, h = 240, 135
+    rgb, ids = sc.render(w, h, seed=1, want_ids=True)
+    assert sc.last_stats.accel_used == rtx.RTX_ACCEL_LBVH
+    ref = oracle.render_scene(sc, w, h, seed=1)
+    assert np.array_equal(ids, ref["ids"]) and sc.last_stats.rays == ref["rays"]
+    assert np.abs(rgb - ref["rgb"]).max() <= 1e-4
+
+
+def test_s3_million_triangles_lbvh_vs_bruteforce_ids(rtx, gpu):
+    """Config C4: 1 002 528-triangle terrain, primary + 4 bounces; hit ids of the LBVH render checked against the
+    brute-force kernel on a 240x135 image (the full-depth brute force is 1e6 tests per ray)."""
+    from rtx_b200 import scenes
+    sc = scenes.terrain(grid=709, rays_per_pixel=1, max_bounces=4)
+    assert sc.object_count == 1_002_529
+    w, h = 240, 135
+    b, ib = sc.render(w, h, seed=1, flags=rtx.RTX_ACCEL_LBVH, want_ids=True)
+    sb = sc.last_stats
+    rays_l, ms_l, npr = sb.rays, sb.device_ms, sb.prims_tested / sb.rays
+    a, ia = sc.render(w, h, seed=1, flags=rtx.RTX_ACCEL_BRUTE, want_ids=True)
+    assert np.array_equal(ia, ib) and a.tobytes() == b.tobytes() and sc.last_stats.rays == rays_l
+    print(f"S3: {rays_l} rays; LBVH {ms_l:.1f} ms ({npr:.1f} prims/ray) vs scan {sc.last_stats.device_ms:.1f} ms")
+    assert (ib != rtx.MISS_ID).mean() > 0.3
