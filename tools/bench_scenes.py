@@ -1,0 +1,83 @@
+#!/usr/bin/env python
+"""bench_scenes.py — the BASELINE.json configs other than the headline (which bench.py owns):
+  C3  S2 10k random spheres, 3840x2160, 16 spp, depth 8        (LBVH)
+  C4  S3 1M-triangle terrain, 1920x1080, 1 spp, primary + 4     (LBVH; ids vs brute force are a test)
+  C5  S1 primary-only 1 spp hit-ID sweep 256^2 .. 7680x4320     (launch/latency-bound regime)
+Prints one JSON line per measurement (device-timed with CUDA events, outputs resident in HBM, scene and
+LBVH built before timing).  Usage: python tools/bench_scenes.py [c3] [c4] [c5] [--quick]
+"""
+import json
+import os
+import sys
+import time
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "rust-raytracing_b200"))
+
+import torch  # noqa: E402
+
+import rtx_b200  # noqa: E402
+from rtx_b200 import scenes  # noqa: E402
+
+
+def timed(scene, w, h, flags, steps, warmup, ids_only=False):
+    dev = torch.device("cuda", 0)
+    rgb = None if ids_only else torch.empty((h, w, 3), dtype=torch.float64, device=dev)
+    ids = torch.empty((h, w), dtype=torch.int32, device=dev)
+    cnt = torch.zeros(8, dtype=torch.int64, device=dev)
+    st = torch.cuda.current_stream(dev)
+    fl = flags | (rtx_b200.RTX_FLAG_NO_RADIANCE if ids_only else 0)
+
+    def go():
+        scene.render_device(w, h, 1, fl, None, rgb.data_ptr() if rgb is not None else None, ids.data_ptr(),
+                            cnt.data_ptr(), st.cuda_stream)
+    t0 = time.perf_counter()
+    go()
+    torch.cuda.synchronize()
+    first = time.perf_counter() - t0
+    for _ in range(warmup):
+        go()
+    torch.cuda.synchronize()
+    cnt.zero_()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(st)
+    for _ in range(steps):
+        go()
+    e1.record(st)
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / steps
+    c = [int(v) // steps for v in cnt.tolist()]
+    return dict(ms_per_frame=ms, rays=c[0], paths=c[1], hits=c[3], nodes_per_ray=c[4] / max(c[0], 1),
+                prims_per_ray=c[5] / max(c[0], 1), mrays_s=c[0] / ms / 1e3, first_call_s=first)
+
+
+def main():
+    which = [a for a in sys.argv[1:] if not a.startswith("-")] or ["c3", "c4", "c5"]
+    quick = "--quick" in sys.argv
+    if "c5" in which:
+        sc = scenes.sphere_demo(rays_per_pixel=1, max_bounces=0)
+        for (w, h) in [(256, 256), (512, 512), (1024, 1024), (1920, 1080), (2048, 2048), (3840, 2160), (4096, 4096),
+                       (7680, 4320)]:
+            r = timed(sc, w, h, rtx_b200.RTX_ACCEL_AUTO, 20, 5, ids_only=True)
+            r.update(config="C5", scene="S1 primary-only hit ids", width=w, height=h, us_per_frame=r["ms_per_frame"] * 1e3,
+                     hbm_gbs=w * h * 4 / (r["ms_per_frame"] * 1e-3) / 1e9)
+            print(json.dumps(r), flush=True)
+    if "c3" in which:
+        sc = scenes.random_spheres(n=10_000, rays_per_pixel=2 if quick else 16, max_bounces=8)
+        w, h = (1920, 1080) if quick else (3840, 2160)
+        r = timed(sc, w, h, rtx_b200.RTX_ACCEL_LBVH, 2, 1)
+        r.update(config="C3", scene="S2 10k spheres", width=w, height=h, spp=sc.config.rays_per_pixel)
+        print(json.dumps(r), flush=True)
+    if "c4" in which:
+        sc = scenes.terrain(grid=709, rays_per_pixel=1, max_bounces=4)
+        w, h = (960, 540) if quick else (1920, 1080)
+        r = timed(sc, w, h, rtx_b200.RTX_ACCEL_LBVH, 2, 1)
+        nodes_b = r["nodes_per_ray"] * 64 + r["prims_per_ray"] * 112
+        r.update(config="C4", scene="S3 1M triangles", width=w, height=h, bytes_per_ray=nodes_b,
+                 traversal_gbs=nodes_b * r["rays"] / (r["ms_per_frame"] * 1e-3) / 1e9)
+        print(json.dumps(r), flush=True)
+
+
+if __name__ == "__main__":
+    main()
