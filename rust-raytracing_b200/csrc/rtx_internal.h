@@ -31,7 +31,7 @@ struct rtx_scene {
   rtx::SceneLayout layout{};
 
   // LBVH: [0] 3-D tree (spheres + triangles), [1..3] prism trees per dropped axis (rtx_lbvh.cuh)
-  rtx::BvhNode* d_bvh[4] = {nullptr, nullptr, nullptr, nullptr};
+  rtx::WideNode* d_bvh[4] = {nullptr, nullptr, nullptr, nullptr};
   uint32_t bvh_root[4] = {0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu};
   uint32_t bvh_count[4] = {0, 0, 0, 0};
   uint32_t bvh_build_launches = 0;

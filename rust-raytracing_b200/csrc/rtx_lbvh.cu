@@ -1,5 +1,5 @@
 // rtx_lbvh.cu — GPU LBVH build (K4): AABBs → Morton codes → radix sort → Karras hierarchy → bottom-up refit
-// → escape pointers.  No reference counterpart (the reference scans all objects, scene.rs:243-251); the gate
+// → two-box f32 traversal nodes.  No reference counterpart (the reference scans all objects, scene.rs:243-251); the gate
 // is "hit ids and distances identical to the brute-force kernel".  Everything here is our own kernel code
 // (no CUB/Thrust): the sort is an 8-bit LSD radix sort, one warp per 1024-key tile, stable by construction.
 #include <cuda_runtime.h>
@@ -269,23 +269,43 @@ __global__ void k_refit(const uint32_t* __restrict__ sorted_vals, const uint32_t
   }
 }
 
-// ---- 6. escape pointers: next node in depth-first order once a subtree is finished ----------------------------
-__global__ void k_escape(int total_nodes, const uint32_t* __restrict__ right, const uint32_t* __restrict__ parent,
-                         BvhNode* __restrict__ nodes) {
-  const int x = blockIdx.x * blockDim.x + threadIdx.x;
-  if (x >= total_nodes) return;
-  uint32_t c = (uint32_t)x;
-  uint32_t esc = BVH_END;
-  for (;;) {
-    const uint32_t p = parent[c];
-    if (p == BVH_END) break;
-    if (right[p] != c) {  // c is a left child: continue with its sibling
-      esc = right[p];
-      break;
+// ---- 7. traversal nodes: both children's boxes (f32, rounded outward) + child refs ----------------------------
+__device__ __forceinline__ uint32_t child_ref(const BvhNode* __restrict__ nodes, uint32_t c) {
+  const uint32_t prim = nodes[c].prim;
+  if (prim == BVH_NO_PRIM) return c;  // internal node index (< m-1 < 2^30)
+  return WIDE_LEAF | (((prim & ~REF_INDEX_MASK) == REF_TRIANGLE) ? WIDE_TRI : 0u) | (prim & REF_INDEX_MASK);
+}
+__global__ void k_emit_wide(int m, const BvhNode* __restrict__ nodes, const uint32_t* __restrict__ left,
+                            const uint32_t* __restrict__ right, WideNode* __restrict__ out) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (m == 1) {  // a single leaf: root = one wide node with an empty second slot
+    if (i != 0) return;
+    WideNode w;
+    for (int k = 0; k < 3; ++k) {
+      w.lo0[k] = __double2float_rd(nodes[0].lo[k]);
+      w.hi0[k] = __double2float_ru(nodes[0].hi[k]);
+      w.lo1[k] = CUDART_INF_F;
+      w.hi1[k] = -CUDART_INF_F;
     }
-    c = p;
+    w.c0 = child_ref(nodes, 0);
+    w.c1 = WIDE_NONE;
+    w.pad[0] = w.pad[1] = 0;
+    out[0] = w;
+    return;
   }
-  nodes[x].escape = esc;
+  if (i >= m - 1) return;
+  const uint32_t l = left[i], r = right[i];
+  WideNode w;
+  for (int k = 0; k < 3; ++k) {
+    w.lo0[k] = __double2float_rd(nodes[l].lo[k]);
+    w.hi0[k] = __double2float_ru(nodes[l].hi[k]);
+    w.lo1[k] = __double2float_rd(nodes[r].lo[k]);
+    w.hi1[k] = __double2float_ru(nodes[r].hi[k]);
+  }
+  w.c0 = child_ref(nodes, l);
+  w.c1 = child_ref(nodes, r);
+  w.pad[0] = w.pad[1] = 0;
+  out[i] = w;
 }
 
 __global__ void k_count_valid(const uint64_t* __restrict__ sorted_keys, uint32_t n, uint32_t* __restrict__ out) {
@@ -313,7 +333,7 @@ struct Tmp {
 
 // Builds one tree over `prims` (host list of REF_*|index).  Synchronous on `stream`.
 static rtx_status build_tree(rtx_scene* s, const std::vector<uint32_t>& prims, int open_axis, const double* d_tri_raw,
-                             cudaStream_t stream, BvhNode** out_nodes, uint32_t* out_root, uint32_t* out_count,
+                             cudaStream_t stream, WideNode** out_nodes, uint32_t* out_root, uint32_t* out_count,
                              uint32_t* launches) {
   *out_nodes = nullptr;
   *out_root = BVH_END;
@@ -370,8 +390,17 @@ static rtx_status build_tree(rtx_scene* s, const std::vector<uint32_t>& prims, i
   for (int k = 0; k < 6; ++k) scale = std::fmax(scale, std::fabs(hb[k]));
   const double pad = scale * 9.5367431640625e-07;  // 2^-20 x scene scale (see rtx_lbvh.cuh)
   const uint32_t total = 2 * m - 1;
-  BvhNode* nodes = nullptr;
+  BvhNode* nodes = nullptr;  // f64 build nodes (freed below); the traversal gets the f32 two-box nodes
+  WideNode* wide = nullptr;
+  const uint32_t n_wide = m > 1 ? m - 1 : 1;
   LBVH_TRY(cudaMalloc((void**)&nodes, (size_t)total * sizeof(BvhNode)));
+  {
+    cudaError_t ew = cudaMalloc((void**)&wide, (size_t)n_wide * sizeof(WideNode));
+    if (ew != cudaSuccess) {
+      cudaFree(nodes);
+      return cuda_fail(s, ew, "lbvh wide nodes");
+    }
+  }
   rtx_status st = RTX_OK;
   do {
     cudaError_t e;
@@ -382,24 +411,25 @@ static rtx_status build_tree(rtx_scene* s, const std::vector<uint32_t>& prims, i
       st = cuda_fail(s, e, "lbvh temporaries");
       break;
     }
-    const unsigned Gm = (m + B - 1) / B, Gt = (total + B - 1) / B;
+    const unsigned Gm = (m + B - 1) / B;
     if (m > 1) k_hierarchy<<<Gm, B, 0, stream>>>(d_keys[cur].p, (int)m, d_left.p, d_right.p, d_parent.p);
     k_refit<<<Gm, B, 0, stream>>>(d_vals[cur].p, d_prims.p, d_lo.p, d_hi.p, (int)m, pad, d_left.p, d_right.p, d_parent.p,
                                   d_flags.p, nodes);
-    if (m > 1) k_escape<<<Gt, B, 0, stream>>>((int)total, d_right.p, d_parent.p, nodes);
+    k_emit_wide<<<Gm, B, 0, stream>>>((int)m, nodes, d_left.p, d_right.p, wide);
     *launches += 3;
     if ((e = cudaGetLastError()) != cudaSuccess || (e = cudaStreamSynchronize(stream)) != cudaSuccess) {
       st = cuda_fail(s, e, "lbvh build kernels");
       break;
     }
   } while (0);
+  cudaFree(nodes);
   if (st != RTX_OK) {
-    cudaFree(nodes);
+    cudaFree(wide);
     return st;
   }
-  *out_nodes = nodes;
-  *out_root = (m == 1) ? 0u : 0u;  // internal root = node 0; with m == 1 the only node (the leaf) is node 0 too
-  *out_count = total;
+  *out_nodes = wide;
+  *out_root = 0u;  // the root is wide node 0
+  *out_count = n_wide;
   return RTX_OK;
 }
 

@@ -4,10 +4,13 @@
 // The LBVH must return EXACTLY what that scan returns: the same distance bits and, among equal distances,
 // the lowest object index.  So the tree only culls; every surviving primitive goes through the same exact
 // f64 distance routine as the brute-force kernel (rtx_trace.cuh), and culling is conservative:
-//  * boxes are f64, padded outward by `pad` (1e-9 x scene scale, ~1e7 x the rounding error of a hit point);
-//  * a node is skipped only if the padded slab interval is empty, ends behind the origin, or starts
-//    beyond the current best distance (strictly: equal distances must still be seen for the tie rule);
-//  * NaN slabs (0 * inf) are ignored by fmin/fmax, i.e. treated as "no constraint".
+//  * boxes are built in f64, padded outward by 2^-20 x scene scale (~1e9 x the rounding error of a hit
+//    point), then rounded OUTWARD to f32;
+//  * the slab test is f32 interval arithmetic with directed rounding (__fsub_rd/_ru, __fmul_rd/_ru) on
+//    rigorous f32 enclosures of the f64 ray, so the computed [entry, exit] always contains the true one —
+//    it runs on the FP32 pipe, leaving the FP64 pipe to the exact leaf tests;
+//  * a child is skipped only if its interval is provably empty, provably behind the origin, or provably
+//    beyond the current best distance (strictly: equal distances must still be seen for the tie rule).
 // Triangles need a second kind of tree.  A "phantom" hit (plane BEHIND the ray, distance = |t|,
 // triangle.rs:118) reports the mirrored point pos + dir*|t|, which is off the plane and only has to lie in
 // the infinite prism over the triangle's projection along the coordinate contains() drops
@@ -30,9 +33,20 @@ struct __align__(16) BvhNode {  // 64 B = four 128-bit loads
   uint32_t pad;
 };
 
+// Traversal node: both children's boxes in f32, rounded OUTWARD from the padded f64 boxes, + child refs.
+// Child ref: bit 31 = leaf; leaf payload: bit 30 = triangle (else sphere), bits 0..29 = index in its array.
+constexpr uint32_t WIDE_LEAF = 0x80000000u, WIDE_TRI = 0x40000000u, WIDE_IDX = 0x3FFFFFFFu;
+constexpr uint32_t WIDE_NONE = 0x7FFFFFFFu;  // empty child slot
+struct __align__(16) WideNode {  // 64 B = four 128-bit loads
+  float lo0[3], hi0[3];
+  float lo1[3], hi1[3];
+  uint32_t c0, c1;
+  uint32_t pad[2];
+};
+
 struct BvhView {
-  const BvhNode* nodes[4];  // [0] 3-D tree over spheres + triangles; [1..3] prism trees (dropped axis x,y,z)
-  uint32_t root[4];         // BVH_END when the tree is empty
+  const WideNode* nodes[4];  // [0] 3-D tree over spheres + triangles; [1..3] prism trees (dropped axis x,y,z)
+  uint32_t root[4];          // BVH_END when the tree is empty, else 0
 };
 
 #if defined(__CUDACC__)
@@ -40,48 +54,119 @@ struct TraversalCounters {
   unsigned long long nodes, prims;
 };
 
-RTX_D void bvh_leaf_test(const SceneView& sc, uint32_t ref, V3 pos, V3 dir, const RayInv& ri, Hit& h,
+// Per-ray f32 interval data for the conservative slab test.  Axes with a negative direction are mirrored
+// (x -> -x), so every component behaves as d >= 0.  o_dn <= o <= o_up and inv_dn <= 1/|d| <= inv_up hold
+// rigorously (directed rounding), inv_dn is finite.
+struct RayF32 {
+  float o_dn[3], o_up[3], inv_dn[3], inv_up[3];
+  bool neg[3];
+};
+RTX_D RayF32 make_ray_f32(V3 pos, V3 dn) {
+  RayF32 r;
+  const double p[3] = {pos.x, pos.y, pos.z}, d[3] = {dn.x, dn.y, dn.z};
+#pragma unroll
+  for (int k = 0; k < 3; ++k) {
+    r.neg[k] = d[k] < 0.0;
+    const double o = r.neg[k] ? -p[k] : p[k];
+    r.o_dn[k] = __double2float_rd(o);
+    r.o_up[k] = __double2float_ru(o);
+    const double inv = 1.0 / fabs(d[k]);  // +inf for d == 0; correctly rounded, so widen by one f32 step each way
+    r.inv_dn[k] = fminf(__double2float_rd(inv * 0.99999999), 3.0e38f);
+    r.inv_up[k] = __double2float_ru(inv * 1.00000001);
+  }
+  return r;
+}
+// Lower bound of the entry parameter and upper bound of the exit parameter of one (mirrored) slab.
+RTX_D void slab(float lo, float hi, bool neg, float o_dn, float o_up, float inv_dn, float inv_up, float& tn, float& tf) {
+  const float l = neg ? -hi : lo, h = neg ? -lo : hi;
+  const float a = __fsub_rd(l, o_up);  // <= l - o
+  const float b = __fsub_ru(h, o_dn);  // >= h - o
+  tn = a < 0.0f ? __fmul_rd(a, inv_up) : __fmul_rd(a, inv_dn);
+  tf = b > 0.0f ? __fmul_ru(b, inv_up) : __fmul_ru(b, inv_dn);
+}
+RTX_D bool box_test(const float* lo, const float* hi, const RayF32& r, float best_up, float& tnear) {
+  float tn0, tf0, tn1, tf1, tn2, tf2;
+  slab(lo[0], hi[0], r.neg[0], r.o_dn[0], r.o_up[0], r.inv_dn[0], r.inv_up[0], tn0, tf0);
+  slab(lo[1], hi[1], r.neg[1], r.o_dn[1], r.o_up[1], r.inv_dn[1], r.inv_up[1], tn1, tf1);
+  slab(lo[2], hi[2], r.neg[2], r.o_dn[2], r.o_up[2], r.inv_dn[2], r.inv_up[2], tn2, tf2);
+  tnear = fmaxf(fmaxf(tn0, tn1), tn2);
+  const float tfar = fminf(fminf(tf0, tf1), tf2);
+  // visit unless provably empty, provably behind the origin, or provably beyond the best distance
+  return !(tfar < fmaxf(tnear, 0.0f)) && !(tnear > best_up);
+}
+
+template <bool PRISM>
+RTX_D void bvh_leaf_test(const SceneView& sc, uint32_t child, V3 pos, V3 dir, const RayInv& ri, Hit& h,
                          uint32_t* panics) {
-  const uint32_t idx = ref & REF_INDEX_MASK;
+  const uint32_t idx = child & WIDE_IDX;
   double t;
-  if ((ref & ~REF_INDEX_MASK) == REF_SPHERE) {
-    if (sphere_distance(sc.sph + (size_t)idx * SPH_STRIDE, pos, ri, &t)) consider(h, t, sc.sph_id[idx], ref);
+  if (!(child & WIDE_TRI)) {
+    if (sphere_distance(sc.sph + (size_t)idx * SPH_STRIDE, pos, ri, &t))
+      consider(h, t, sc.sph_id[idx], REF_SPHERE | idx);
   } else {
+    const double* rec = sc.tri + (size_t)idx * TRI_STRIDE;
+    if (PRISM) {
+      // The prism trees only have to find PHANTOM hits (plane behind the ray: the quotient of
+      // triangle.rs:34 is negative); a plane in front puts the hit point on the triangle, inside its 3-D
+      // box, where the 3-D tree finds it.  Same two dot products triangle_distance starts with.
+      const V3 n = mk3(rec[3], rec[4], rec[5]);
+      const double num = dot(n, mk3(rec[0], rec[1], rec[2]) - pos), den = dot(ri.dn, n);
+      if ((num > 0.0 && den > 0.0) || (num < 0.0 && den < 0.0)) return;
+    }
     bool panic = false;
-    if (triangle_distance(sc.tri + (size_t)idx * TRI_STRIDE, pos, dir, ri, &t, &panic))
-      consider(h, t, sc.tri_id[idx], ref);
+    if (triangle_distance(rec, pos, dir, ri, &t, &panic)) consider(h, t, sc.tri_id[idx], REF_TRIANGLE | idx);
     if (panic) ++*panics;
   }
 }
 
-// Skip-pointer ("escape index") walk: no stack, fixed depth-first order.
-RTX_D void bvh_walk(const BvhNode* __restrict__ nodes, uint32_t root, const SceneView& sc, V3 pos, V3 dir,
-                    const RayInv& ri, V3 inv, Hit& h, uint32_t* panics, TraversalCounters& tc) {
-  uint32_t cur = root;
-  while (cur != BVH_END) {
-    const BvhNode* nd = nodes + cur;
-    const double2 a0 = __ldg(reinterpret_cast<const double2*>(nd));      // four 128-bit loads per node
-    const double2 a1 = __ldg(reinterpret_cast<const double2*>(nd) + 1);
-    const double2 b = __ldg(reinterpret_cast<const double2*>(nd) + 2);
-    const uint4 c = __ldg(reinterpret_cast<const uint4*>(nd) + 3);       // left escape prim pad
-    struct { double x, y, z, w; } a = {a0.x, a0.y, a1.x, a1.y};          // lo.xyz hi.x ; b = hi.yz
-    ++tc.nodes;
-    const double t1x = (a.x - pos.x) * inv.x, t2x = (a.w - pos.x) * inv.x;
-    const double t1y = (a.y - pos.y) * inv.y, t2y = (b.x - pos.y) * inv.y;
-    const double t1z = (a.z - pos.z) * inv.z, t2z = (b.y - pos.z) * inv.z;
-    const double tmin = fmax(fmax(fmin(t1x, t2x), fmin(t1y, t2y)), fmin(t1z, t2z));
-    const double tmax = fmin(fmin(fmax(t1x, t2x), fmax(t1y, t2y)), fmax(t1z, t2z));
-    // !(miss) form so that a NaN tmin/tmax (all three slabs NaN) falls through to "visit"
-    const bool miss = (tmax < fmax(tmin, 0.0)) || (tmin > h.t);
-    if (miss) {
-      cur = c.y;
-    } else if (c.z != BVH_NO_PRIM) {
+// Near-first walk with a short per-thread stack of (child ref, entry bound).
+template <bool PRISM>
+RTX_D void bvh_walk(const WideNode* __restrict__ nodes, const SceneView& sc, V3 pos, V3 dir, const RayInv& ri,
+                    const RayF32& rf, Hit& h, uint32_t* panics, TraversalCounters& tc) {
+  uint32_t stack_ref[128];
+  float stack_t[128];
+  int sp = 0;
+  uint32_t cur = 0;  // root
+  for (;;) {
+    if (cur & WIDE_LEAF) {
       ++tc.prims;
-      bvh_leaf_test(sc, c.z, pos, dir, ri, h, panics);
-      cur = c.y;
+      bvh_leaf_test<PRISM>(sc, cur, pos, dir, ri, h, panics);
     } else {
-      cur = c.x;
+      const WideNode* nd = nodes + cur;
+      const float4 q0 = __ldg(reinterpret_cast<const float4*>(nd));
+      const float4 q1 = __ldg(reinterpret_cast<const float4*>(nd) + 1);
+      const float4 q2 = __ldg(reinterpret_cast<const float4*>(nd) + 2);
+      const uint4 q3 = __ldg(reinterpret_cast<const uint4*>(nd) + 3);
+      ++tc.nodes;
+      const float lo0[3] = {q0.x, q0.y, q0.z}, hi0[3] = {q0.w, q1.x, q1.y};
+      const float lo1[3] = {q1.z, q1.w, q2.x}, hi1[3] = {q2.y, q2.z, q2.w};
+      const float best_up = __double2float_ru(h.t);
+      float t0, t1;
+      const bool v0 = box_test(lo0, hi0, rf, best_up, t0);
+      const bool v1 = box_test(lo1, hi1, rf, best_up, t1);
+      if (v0 && v1) {
+        const bool first0 = t0 <= t1;
+        // depth <= 64 key bits + 32 index bits (Karras: every level lengthens the common prefix), so 128 holds
+        stack_ref[sp] = first0 ? q3.y : q3.x;
+        stack_t[sp] = first0 ? t1 : t0;
+        ++sp;
+        cur = first0 ? q3.x : q3.y;
+        continue;
+      } else if (v0) {
+        cur = q3.x;
+        continue;
+      } else if (v1) {
+        cur = q3.y;
+        continue;
+      }
     }
+    // pop, dropping entries that can no longer beat the best distance
+    for (;;) {
+      if (sp == 0) return;
+      --sp;
+      if (!(stack_t[sp] > __double2float_ru(h.t))) break;
+    }
+    cur = stack_ref[sp];
   }
 }
 
@@ -100,10 +185,11 @@ RTX_D Hit closest_lbvh(const SceneView& sc, const BvhView& bv, V3 pos, V3 dir, u
   }
   tc.prims += sc.n_pl;
   // slab parameters are in units of dn, like every distance the shapes return
-  const V3 inv = mk3(1.0 / ri.dn.x, 1.0 / ri.dn.y, 1.0 / ri.dn.z);
+  const RayF32 rf = make_ray_f32(pos, ri.dn);
+  if (bv.root[0] != BVH_END) bvh_walk<false>(bv.nodes[0], sc, pos, dir, ri, rf, h, panics, tc);
 #pragma unroll 1
-  for (int k = 0; k < 4; ++k)
-    if (bv.root[k] != BVH_END) bvh_walk(bv.nodes[k], bv.root[k], sc, pos, dir, ri, inv, h, panics, tc);
+  for (int k = 1; k < 4; ++k)
+    if (bv.root[k] != BVH_END) bvh_walk<true>(bv.nodes[k], sc, pos, dir, ri, rf, h, panics, tc);
   return h;
 }
 #endif
