@@ -182,6 +182,9 @@ rtx_status rtx_debug_normal_at(rtx_scene* scene, const uint32_t* ids, const doub
 rtx_status rtx_debug_random_bounce_dir(int32_t device, uint64_t* states, const double* in, uint64_t n, double* out);
 /* ≙ fastrand::f64()                   call sites math/vector.rs:31-33,37-38 — n draws from *state   */
 rtx_status rtx_debug_wyrand_f64(int32_t device, uint64_t* state, uint64_t n, double* out);
+/* ≙ Vector3 / f64                      math/vector/div.rs:11-21 — the device's shared-reciprocal form
+ * (out) next to three plain IEEE divisions (ref); a[n][3], s[n] → out[n][3], ref[n][3]              */
+rtx_status rtx_debug_vdiv3(int32_t device, const double* a, const double* s, uint64_t n, double* out, double* ref);
 /* Returns fl(fl(a*b)+c) as the library's device code computes `a*b+c`: proves no FMA contraction.  */
 rtx_status rtx_debug_contraction_probe(int32_t device, double a, double b, double c, double* out);
 /* The seeding convention: WyRand state of the stream with the given key. */

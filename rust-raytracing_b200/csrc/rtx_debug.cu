@@ -52,6 +52,17 @@ __global__ void wyrand_kernel(uint64_t* state, uint64_t n, double* __restrict__ 
   *state = g.s;
 }
 
+// vdiv3 (shared-reciprocal division, rtx_math.cuh) next to three plain __ddiv_rn: must be bit-equal.
+__global__ void vdiv3_kernel(const double* __restrict__ a, const double* __restrict__ s, uint64_t n,
+                             double* __restrict__ out, double* __restrict__ ref) {
+  const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const V3 v = mk3(a[i * 3], a[i * 3 + 1], a[i * 3 + 2]);
+  const V3 q = vdiv3(v, s[i]);
+  out[i * 3 + 0] = q.x, out[i * 3 + 1] = q.y, out[i * 3 + 2] = q.z;
+  ref[i * 3 + 0] = __ddiv_rn(v.x, s[i]), ref[i * 3 + 1] = __ddiv_rn(v.y, s[i]), ref[i * 3 + 2] = __ddiv_rn(v.z, s[i]);
+}
+
 // Register-resident issue-rate probes.  8 independent chains per thread.
 template <bool FUSED>
 __global__ void __launch_bounds__(256) fp64_probe_kernel(double* out, int iters, double a, double b) {
@@ -193,6 +204,25 @@ rtx_status rtx_debug_wyrand_f64(int32_t device, uint64_t* state, uint64_t n, dou
   RTX_CUDA_TRY(nullptr, cudaGetLastError());
   RTX_CUDA_TRY(nullptr, cudaMemcpy(out, d_out.p, n * 8, cudaMemcpyDeviceToHost));
   RTX_CUDA_TRY(nullptr, cudaMemcpy(state, d_state.p, 8, cudaMemcpyDeviceToHost));
+  return RTX_OK;
+}
+
+rtx_status rtx_debug_vdiv3(int32_t device, const double* a, const double* s, uint64_t n, double* out, double* ref) {
+  if (!a || !s || !out || !ref) return fail(nullptr, RTX_ERR_INVALID_ARGUMENT, "null argument");
+  rtx_status st = pick_device(device);
+  if (st != RTX_OK) return st;
+  if (n == 0) return RTX_OK;
+  DevBuf<double> d_a, d_s, d_out, d_ref;
+  RTX_CUDA_TRY(nullptr, d_a.alloc(n * 3));
+  RTX_CUDA_TRY(nullptr, d_s.alloc(n));
+  RTX_CUDA_TRY(nullptr, d_out.alloc(n * 3));
+  RTX_CUDA_TRY(nullptr, d_ref.alloc(n * 3));
+  RTX_CUDA_TRY(nullptr, cudaMemcpy(d_a.p, a, n * 24, cudaMemcpyHostToDevice));
+  RTX_CUDA_TRY(nullptr, cudaMemcpy(d_s.p, s, n * 8, cudaMemcpyHostToDevice));
+  vdiv3_kernel<<<(unsigned)((n + 127) / 128), 128>>>(d_a.p, d_s.p, n, d_out.p, d_ref.p);
+  RTX_CUDA_TRY(nullptr, cudaGetLastError());
+  RTX_CUDA_TRY(nullptr, cudaMemcpy(out, d_out.p, n * 24, cudaMemcpyDeviceToHost));
+  RTX_CUDA_TRY(nullptr, cudaMemcpy(ref, d_ref.p, n * 24, cudaMemcpyDeviceToHost));
   return RTX_OK;
 }
 

@@ -141,13 +141,20 @@ RTX_D void consider(Hit& h, double t, uint32_t id, uint32_t ref) {
 // (-h - sqrt(q)) / a — every intermediate differs from the reference's by an exact power of two, the
 // result by nothing.  `disc <= 1e-100` becomes `q <= 1e-100/4`.  h >= 0 gives a negative t, which
 // scene.rs:249 drops; testing it first skips the sqrt + division.
-RTX_D bool sphere_distance(const double* __restrict__ rec, V3 pos, const RayInv& ri, double* out_t) {
+RTX_D bool sphere_candidate(const double* __restrict__ rec, V3 pos, const RayInv& ri, double* out_h, double* out_q) {
   const V3 o = pos - mk3(rec[0], rec[1], rec[2]);
   const double h = dot(o, ri.dn);
   const double c = fsub(dot(o, o), rec[3]);
   const double q = fsub(fmul(h, h), fmul(ri.a, c));
-  if (q > (1e-100 * 0.25) && h < 0.0) {
-    *out_t = fdiv(fsub(-h, fsqrt(q)), ri.a);
+  *out_h = h;
+  *out_q = q;
+  return q > (1e-100 * 0.25) && h < 0.0;
+}
+RTX_D double sphere_root(double h, double q, const RayInv& ri) { return fdiv(fsub(-h, fsqrt(q)), ri.a); }
+RTX_D bool sphere_distance(const double* __restrict__ rec, V3 pos, const RayInv& ri, double* out_t) {
+  double h, q;
+  if (sphere_candidate(rec, pos, ri, &h, &q)) {
+    *out_t = sphere_root(h, q, ri);
     return true;
   }
   return false;
@@ -204,10 +211,21 @@ RTX_D Hit closest_brute(const SceneView& sc, V3 pos, V3 dir, uint32_t* panics) {
   h.id = MISS_ID;
   h.ref = 0;
   const RayInv ri = ray_invariants(dir);
+  // A sphere that passes the discriminant/sign test still needs a sqrt and a division for its root.  Few
+  // spheres pass per ray, at different loop trips in different lanes, so the root is deferred: a lane keeps
+  // one pending candidate and resolves it when a second one turns up or after the loop — where the lanes
+  // of a warp meet again.  `consider` is a lexicographic (t, id) minimum, so the order is irrelevant.
+  bool pend = false;
+  double pend_h = 0.0, pend_q = 0.0;
+  uint32_t pend_i = 0;
   for (uint32_t i = 0; i < sc.n_sph; ++i) {
-    double t;
-    if (sphere_distance(sc.sph + (size_t)i * SPH_STRIDE, pos, ri, &t)) consider(h, t, sc.sph_id[i], REF_SPHERE | i);
+    double hh, qq;
+    if (sphere_candidate(sc.sph + (size_t)i * SPH_STRIDE, pos, ri, &hh, &qq)) {
+      if (pend) consider(h, sphere_root(pend_h, pend_q, ri), sc.sph_id[pend_i], REF_SPHERE | pend_i);
+      pend = true, pend_h = hh, pend_q = qq, pend_i = i;
+    }
   }
+  if (pend) consider(h, sphere_root(pend_h, pend_q, ri), sc.sph_id[pend_i], REF_SPHERE | pend_i);
   for (uint32_t i = 0; i < sc.n_pl; ++i) {
     double t;
     if (plane_distance(sc.pl + (size_t)i * PL_STRIDE, pos, ri, &t)) consider(h, t, sc.pl_id[i], REF_PLANE | i);

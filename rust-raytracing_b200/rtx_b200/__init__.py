@@ -430,6 +430,16 @@ def debug_random_bounce_dir(states, inputs, device=0):
     return out, states
 
 
+def debug_vdiv3(a, s, device=0):
+    """(shared-reciprocal quotient, three plain IEEE divisions) of a[n][3] / s[n] on the device."""
+    a = np.ascontiguousarray(a, dtype=np.float64).reshape(-1, 3)
+    s = np.ascontiguousarray(s, dtype=np.float64).reshape(-1)
+    out, ref = np.empty_like(a), np.empty_like(a)
+    _abi.check(_abi.load().rtx_debug_vdiv3(device, a.ctypes.data, s.ctypes.data, a.shape[0], out.ctypes.data,
+                                           ref.ctypes.data))
+    return out, ref
+
+
 def debug_contraction_probe(a, b, c, device=0):
     out = C.c_double()
     _abi.check(_abi.load().rtx_debug_contraction_probe(device, a, b, c, C.byref(out)))

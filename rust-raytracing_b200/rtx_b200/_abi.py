@@ -109,6 +109,7 @@ SIGNATURES = {
     "rtx_debug_normal_at": (C.c_int32, [_vp, _vp, _vp, C.c_uint64, _vp]),
     "rtx_debug_random_bounce_dir": (C.c_int32, [C.c_int32, _vp, _vp, C.c_uint64, _vp]),
     "rtx_debug_wyrand_f64": (C.c_int32, [C.c_int32, _P(C.c_uint64), C.c_uint64, _vp]),
+    "rtx_debug_vdiv3": (C.c_int32, [C.c_int32, _vp, _vp, C.c_uint64, _vp, _vp]),
     "rtx_debug_contraction_probe": (C.c_int32, [C.c_int32, C.c_double, C.c_double, C.c_double, _P(C.c_double)]),
     "rtx_stream_state": (C.c_uint64, [C.c_uint64, C.c_uint64]),
 }
