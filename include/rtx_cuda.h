@@ -69,7 +69,9 @@ enum {
   RTX_ACCEL_BRUTE     = 1u,       /* scene.rs:243-251 as written: O(N) scan                          */
   RTX_ACCEL_LBVH      = 2u,       /* GPU-built Morton LBVH; identical results to RTX_ACCEL_BRUTE     */
   RTX_ACCEL_MASK      = 3u,
-  RTX_FLAG_NO_RADIANCE = 4u       /* hit-ID-only render (out_rgb may be NULL)                        */
+  RTX_FLAG_NO_RADIANCE = 4u,      /* hit-ID-only render (out_rgb may be NULL)                        */
+  RTX_FLAG_LANE_KERNEL = 8u       /* force the one-pixel-per-lane kernel where the context-pool kernel
+                                     would run (same image; for A/B tests and measurements)            */
 };
 
 /* Per-render statistics (all ranks report their own shard). */

@@ -228,6 +228,7 @@ static rtx_status render_common(rtx_scene* s, uint32_t width, uint32_t height, u
   p.scene_blob = s->d_blob;
   p.layout = s->layout;
   p.use_bvh = use_bvh ? 1u : 0u;
+  p.lane_kernel = (flags & RTX_FLAG_LANE_KERNEL) ? 1u : 0u;
   for (int k = 0; k < 4; ++k) {
     p.bvh.nodes[k] = use_bvh ? s->d_bvh[k] : nullptr;
     p.bvh.root[k] = use_bvh ? s->bvh_root[k] : BVH_END;

@@ -67,6 +67,9 @@ rtx_status ensure_uploaded(rtx_scene* s, cudaStream_t stream);
 // Builds (or reuses) the sin/cos tables for this image size.  Asynchronous on `stream`.
 rtx_status ensure_tables(rtx_scene* s, uint32_t width, uint32_t height, cudaStream_t stream);
 cudaError_t launch_render(const RenderParams& p, int sm_count, cudaStream_t stream, uint32_t* out_launches);
+// rtx_render_pool.cu: the context-pool kernel for scanned, shared-memory-resident scenes
+bool pool_kernel_eligible(const RenderParams& p);
+cudaError_t launch_render_pool(const RenderParams& p, int sm_count, cudaStream_t stream, uint32_t* out_launches);
 // Builds the LBVH trees if the object list changed since the last build.  Synchronous.
 rtx_status ensure_lbvh(rtx_scene* s, cudaStream_t stream);
 void free_lbvh(rtx_scene* s);

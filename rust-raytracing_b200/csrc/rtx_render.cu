@@ -18,6 +18,7 @@
 #include <cuda_runtime.h>
 #include <math_constants.h>
 
+#include "rtx_internal.h"
 #include "rtx_lbvh.cuh"
 #include "rtx_render.cuh"
 #include "rtx_trace.cuh"
@@ -26,39 +27,6 @@ namespace rtx {
 
 constexpr int RENDER_BLOCK = 256;
 constexpr uint32_t FULL = 0xFFFFFFFFu;
-
-// ---- TMA bulk copy (global → shared) with an mbarrier ------------------------------------------
-__device__ __forceinline__ uint32_t smem_u32(const void* p) {
-  return (uint32_t)__cvta_generic_to_shared(p);
-}
-__device__ __forceinline__ void stage_blob(unsigned char* dst, const unsigned char* src, uint32_t bytes,
-                                           uint64_t* mbar) {
-  const uint32_t bar = smem_u32(mbar);
-  if (threadIdx.x == 0) {
-    asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar));
-    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-  }
-  __syncthreads();
-  if (threadIdx.x == 0) {
-    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
-    asm volatile(
-        "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
-            smem_u32(dst)),
-        "l"(src), "r"(bytes), "r"(bar)
-        : "memory");
-  }
-  // every thread waits for phase 0 of the barrier
-  asm volatile(
-      "{\n"
-      ".reg .pred P1;\n"
-      "WAIT_LOOP:\n"
-      "mbarrier.try_wait.parity.shared::cta.b64 P1, [%0], 0;\n"
-      "@P1 bra DONE;\n"
-      "bra WAIT_LOOP;\n"
-      "DONE:\n"
-      "}\n" ::"r"(bar)
-      : "memory");
-}
 
 template <bool SMEM_SCENE, bool USE_BVH>
 __global__ void __launch_bounds__(RENDER_BLOCK, 2) render_megakernel(const __grid_constant__ RenderParams p) {
@@ -250,6 +218,7 @@ __global__ void __launch_bounds__(RENDER_BLOCK, 2) render_megakernel(const __gri
 
 // Launch helper used by the API layer.  Returns the cudaError of the launch.
 cudaError_t launch_render(const RenderParams& p, int sm_count, cudaStream_t stream, uint32_t* out_launches) {
+  if (!p.lane_kernel && pool_kernel_eligible(p)) return launch_render_pool(p, sm_count, stream, out_launches);
   constexpr uint32_t SMEM_LIMIT = 64u * 1024u;
   const bool use_smem = p.layout.bytes > 0 && p.layout.bytes <= SMEM_LIMIT;
   const size_t smem = use_smem ? (size_t)p.layout.bytes + 128 : 0;

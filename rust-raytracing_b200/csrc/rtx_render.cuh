@@ -32,6 +32,7 @@ struct RenderParams {
   SceneLayout layout;
   BvhView bvh;       // used when use_bvh != 0
   uint32_t use_bvh;
+  uint32_t lane_kernel;  // RTX_FLAG_LANE_KERNEL: never pick the context-pool kernel
   // image shard
   uint32_t shard_index, shard_count;
   uint32_t tiles_x, tiles_y;
@@ -43,5 +44,41 @@ struct RenderParams {
   uint32_t* out_ids;                // may be null
   unsigned long long* ray_counter;  // [0] rays, [1] paths, [2] triangle panics, [3] hits, [4] nodes visited, [5] prims tested; may be null
 };
+
+#if defined(__CUDACC__)
+// ---- TMA bulk copy (global → shared) with an mbarrier ------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void* p) {
+  return (uint32_t)__cvta_generic_to_shared(p);
+}
+__device__ __forceinline__ void stage_blob(unsigned char* dst, const unsigned char* src, uint32_t bytes,
+                                           uint64_t* mbar) {
+  const uint32_t bar = smem_u32(mbar);
+  if (threadIdx.x == 0) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar));
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+    asm volatile(
+        "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+            smem_u32(dst)),
+        "l"(src), "r"(bytes), "r"(bar)
+        : "memory");
+  }
+  // every thread waits for phase 0 of the barrier
+  asm volatile(
+      "{\n"
+      ".reg .pred P1;\n"
+      "WAIT_LOOP:\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 P1, [%0], 0;\n"
+      "@P1 bra DONE;\n"
+      "bra WAIT_LOOP;\n"
+      "DONE:\n"
+      "}\n" ::"r"(bar)
+      : "memory");
+}
+
+#endif  // __CUDACC__
 
 }  // namespace rtx

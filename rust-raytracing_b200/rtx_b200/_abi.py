@@ -67,6 +67,7 @@ RTX_ERR_OUT_OF_MEMORY = 3
 RTX_ERR_UNSUPPORTED_SHAPE = 4
 RTX_ACCEL_AUTO, RTX_ACCEL_BRUTE, RTX_ACCEL_LBVH = 0, 1, 2
 RTX_FLAG_NO_RADIANCE = 4
+RTX_FLAG_LANE_KERNEL = 8
 RTX_TILE = 16
 MISS_ID = 0xFFFFFFFF
 

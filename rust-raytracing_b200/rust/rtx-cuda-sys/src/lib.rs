@@ -44,6 +44,7 @@ pub type rtx_status = i32;
 pub const RTX_OK: rtx_status = 0;
 pub const RTX_ACCEL_AUTO: u32 = 0;
 pub const RTX_FLAG_NO_RADIANCE: u32 = 4;
+pub const RTX_FLAG_LANE_KERNEL: u32 = 8;
 
 extern "C" {
     pub fn rtx_camera_new(position: *const rtx_vec3, direction: *const rtx_vec3, fov: f64, out: *mut rtx_camera) -> rtx_status;

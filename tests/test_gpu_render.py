@@ -178,3 +178,30 @@ def test_cpp_host_mirror(gpu):
     out = subprocess.run([exe], capture_output=True, text=True, timeout=300)
     print(out.stdout[-2000:], out.stderr[-2000:])
     assert out.returncode == 0 and "ALL OK" in out.stdout
+
+
+def test_context_pool_kernel_equals_lane_kernel(rtx, gpu):
+    """The two schedulers of the same arithmetic (rtx_render_pool.cu: 64 pixel contexts per warp in three state
+    masks; rtx_render.cu: one pixel per lane) must produce the same bytes, ids, and counters — on spheres,
+    planes and triangles, at ragged sizes, at 0 spp, at depth 0, and when sharded."""
+    from rtx_b200 import Camera, Config, Material, Object, Plane, Scene, Sphere, Triangle, scenes
+    BR, LANE = rtx.RTX_ACCEL_BRUTE, rtx.RTX_ACCEL_BRUTE | rtx.RTX_FLAG_LANE_KERNEL
+    cases = []
+    for spp, depth, w, h in [(4, 8, 333, 77), (1, 0, 17, 5), (3, 2, 1, 1), (0, 8, 40, 30), (16, 8, 256, 144)]:
+        cases.append((scenes.sphere_demo(rays_per_pixel=spp, max_bounces=depth), w, h))
+    tri = Scene(Config().with_rays_per_pixel(3).with_max_bounces(4), Camera((0, 0, 1), (1, 0, 0.2), 1.2))
+    tri.add_object(Object(Triangle([(4, -2, 3), (8, 0, 3.5), (4, 2, 3)]), Material((0.7, 0.7, 0.2), (0, 0, 0), 0.3)))
+    tri.add_object(Object(Plane((0, 0, 0), (0, 0, 1)), Material.colored((0.5, 0.5, 0.5))))
+    tri.add_object(Object(Triangle([(5, -3, 0.1), (5, 3, 0.1), (7, 1, 2)]), Material((0.2, 0.7, 0.9), (0, 0, 0), 1.0)))
+    tri.add_object(Object(Sphere((6, 0, 9), 4), Material.light((3, 3, 3))))
+    cases.append((tri, 320, 200))
+    cases.append((scenes.random_spheres(n=100, rays_per_pixel=2, max_bounces=8), 200, 120))  # 7 KB blob
+    empty = Scene(Config().with_rays_per_pixel(2), Camera((0, 0, 0), (1, 0, 0), 1.0))
+    for sc, w, h in cases:
+        a, ia = sc.render(w, h, seed=5, flags=BR, want_ids=True)
+        sa = (sc.last_stats.rays, sc.last_stats.paths, sc.last_stats.hits, sc.last_stats.prims_tested)
+        b, ib = sc.render(w, h, seed=5, flags=LANE, want_ids=True)
+        sb = (sc.last_stats.rays, sc.last_stats.paths, sc.last_stats.hits, sc.last_stats.prims_tested)
+        assert a.tobytes() == b.tobytes() and np.array_equal(ia, ib) and sa == sb, (w, h, sa, sb)
+    a = empty.render(33, 9, seed=1)
+    assert not a.any()
