@@ -36,6 +36,10 @@ def parse_args():
     ap.add_argument("--steps", type=int, default=60)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--gather", default="p2p", choices=["p2p", "nccl"],
+                    help="N>1: p2p = peers store pixels into rank 0's frame from inside the render kernel "
+                         "(NVLink peer memory) + one tiny all-reduce as completion barrier; nccl = compact shard "
+                         "buffers + dist.gather + de-interleave kernel")
     ap.add_argument("--width", type=int, default=WIDTH)
     ap.add_argument("--height", type=int, default=HEIGHT)
     ap.add_argument("--spp", type=int, default=SPP)
@@ -188,8 +192,11 @@ def run_b200(args):
     if world == 1:
         rgb = torch.empty((H, W, 3), dtype=torch.float64, device=dev)
         ids = torch.empty((H, W), dtype=torch.int32, device=dev)
-    else:
+    elif args.gather == "nccl":
         rgb_c, ids_c = rdist.alloc_shard_buffers(W, H, world, dev, want_ids=True)
+    else:
+        frame = rdist.PeerFrame(W, H, local_rank, None, 0, want_ids=True)
+        frame_rgb = frame.tensors()[0] if rank == 0 else None
 
     def step(seed):
         """One pass of the hot path over the whole image, outputs resident in HBM (on rank 0 for N > 1)."""
@@ -197,6 +204,10 @@ def run_b200(args):
             scene.render_device(W, H, seed, rtx_b200.RTX_ACCEL_AUTO, None, rgb.data_ptr(), ids.data_ptr(),
                                 counters.data_ptr(), stream.cuda_stream)
             return rgb
+        if args.gather == "p2p":
+            # gather fused into the render kernel: peers store finished pixels into rank 0's frame over NVLink
+            frame.render(scene, seed, counters)
+            return frame_rgb
         rdist.render_shard(scene, W, H, seed, rank, world, rgb_c, ids_c, counters)
         g_rgb = rdist.gather_shards(rgb_c)
         g_ids = rdist.gather_shards(ids_c)
@@ -216,11 +227,14 @@ def run_b200(args):
     sampler = ClockSampler(local_rank)
     if rank == 0:
         sampler.start()
+    align = torch.zeros(1, dtype=torch.int32, device=dev)
     ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(K)]
     sync_all()
     t_wall0 = time.perf_counter()
     for i in range(K):
         flush_buf.zero_()  # L2 flush between timed iterations (outside the event pair)
+        if world > 1:
+            dist.all_reduce(align)  # ranks leave the flush together: skew between ranks is not render time
         ev[i][0].record(stream)
         step(SEED)
         ev[i][1].record(stream)
@@ -275,16 +289,20 @@ def run_b200(args):
     e2e = {"value": rays_per_step * K / float(te.item()) / 1e6, "unit": "Mrays/s",
            "h2d_bytes_per_step": int(blob_bytes), "d2h_bytes_per_step": int(npix * 24 + 32),
            "api": "rtx_scene_render (host buffers, pinned)" if world == 1 else
-                  "rtx_scene_render_device per rank + NCCL gather + rtx_deinterleave_tiles + D2H on rank 0",
+                  ("rtx_scene_render_device per rank (RTX_FLAG_SHARD_IN_PLACE into rank 0's peer frame) + D2H on rank 0"
+                   if args.gather == "p2p" else
+                   "rtx_scene_render_device per rank + NCCL gather + rtx_deinterleave_tiles + D2H on rank 0"),
            "ms_per_step": float(te.item()) / K * 1e3}
 
+    if world > 1 and args.gather == "p2p":
+        frame.close()
     if rank != 0:
         if world > 1:
             dist.barrier()
             dist.destroy_process_group()
         return
 
-    # ---- roofline of the dominant kernel (render_megakernel), measured live ----
+    # ---- roofline of the dominant kernel (render_pool_kernel for S1), measured live ----
     nf_tf, fma_tf = rtx_b200.probe_fp64_peak(local_rank)
     flops, per_ray = algorithmic_flops(scene, rays, hits, paths)
     # at N > 1 dev_ms contains the gather; the kernel-only figure is quoted at N = 1
@@ -299,7 +317,7 @@ def run_b200(args):
     roofline = {
         "bound": "fp64", "achieved": achieved, "peak": nf_tf, "unit": "TFLOP/s", "frac": achieved / nf_tf if nf_tf else None,
         "traffic": None,
-        "kernel": "rtx::render_megakernel<true>", "launches": K, "avg_launch_ms": dev_ms / K,
+        "kernel": "rtx::render_pool_kernel (context-pool scheduler; S1 blob <= 16 KB, scanned from shared memory)", "launches": K, "avg_launch_ms": dev_ms / K,
         "model": f"flops = rays*{per_ray} + 92*hits + 27*paths (FP64, non-fused; SURVEY.md 8d); div/sqrt/sincos count 1 each",
         "peak_source": "measured live: rtx_probe_fp64_peak non-fused DADD+DMUL issue rate (MEASURED_PEAKS.json has no FP64 figure)",
         "fp64_fma_peak_tflops": fma_tf,
@@ -313,14 +331,17 @@ def run_b200(args):
         cpu_baseline = cpu_render_rate(W, H, args.cpu_seconds)
         for k in ("seconds", "rays", "spp"):
             cpu_baseline.pop(k)
-    launches_per_step = 1 if world == 1 else 2  # render kernel (+ de-interleave on rank 0); NCCL's are not ours
+    # render kernel per rank (+ de-interleave on rank 0 with --gather nccl); NCCL's kernels are not ours
+    launches_per_step = world if (world == 1 or args.gather == "p2p") else world + 1
     print(json.dumps({
         "metric": METRIC, "value": value, "unit": "Mrays/s", "n_gpus": world, "steps": K, "warmup": WU,
         "ms_per_step": dev_ms / K, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
         "dtype": "f64", "data": "synthetic",
         "config": {"workload": WORKLOAD, "width": W, "height": H, "spp": args.spp, "max_bounces": MAX_BOUNCES,
                    "seed": SEED, "parallelism": f"image tiles 16x16 interleaved over {world} GPU(s)" +
-                   ("" if world == 1 else ", NCCL gather to rank 0 inside the step"),
+                   ("" if world == 1 else (", pixels stored into rank 0's frame by the render kernel over NVLink "
+                                           "peer memory + 4-byte all-reduce as completion barrier, inside the step"
+                                           if args.gather == "p2p" else ", NCCL gather to rank 0 inside the step")),
                    "l2": "flushed between timed iterations (256 MB memset outside the event pairs)",
                    "rays_per_step": rays_per_step, "hits_per_step": hits // K, "paths_per_step": paths // K},
         "e2e": e2e, "gpu_launches": launches_per_step * K, "roofline": roofline, "cpu_baseline": cpu_baseline,

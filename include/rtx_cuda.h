@@ -70,8 +70,13 @@ enum {
   RTX_ACCEL_LBVH      = 2u,       /* GPU-built Morton LBVH; identical results to RTX_ACCEL_BRUTE     */
   RTX_ACCEL_MASK      = 3u,
   RTX_FLAG_NO_RADIANCE = 4u,      /* hit-ID-only render (out_rgb may be NULL)                        */
-  RTX_FLAG_LANE_KERNEL = 8u       /* force the one-pixel-per-lane kernel where the context-pool kernel
+  RTX_FLAG_LANE_KERNEL = 8u,      /* force the one-pixel-per-lane kernel where the context-pool kernel
                                      would run (same image; for A/B tests and measurements)            */
+  RTX_FLAG_SHARD_IN_PLACE = 16u   /* with shard->count > 1: write this shard's pixels at their final
+                                     position of the FULL image layout instead of a compact buffer.
+                                     d_out_* may then be another GPU's memory (rtx_peer_open): every
+                                     rank stores straight into rank 0's frame over NVLink while it
+                                     renders — the gather of scene.rs:167-169 fused into the kernel   */
 };
 
 /* Per-render statistics (all ranks report their own shard). */
@@ -150,6 +155,19 @@ uint64_t   rtx_shard_tile_count(uint32_t width, uint32_t height, uint32_t index,
 rtx_status rtx_deinterleave_tiles(uint32_t width, uint32_t height, uint32_t count,
                                   const void* d_gathered_rgb, void* d_out_rgb,
                                   const void* d_gathered_ids, void* d_out_ids, void* cuda_stream);
+
+/* ---- peer frame buffers (multi-GPU, one process per GPU) ------------------------------------------
+ * The owner (rank 0) allocates the frame with rtx_peer_alloc and exports a 64-byte handle; the other
+ * processes of the node open it and pass the returned pointer as d_out_rgb / d_out_primary_hit_id of
+ * rtx_scene_render_device together with RTX_FLAG_SHARD_IN_PLACE.  Their render kernels then write
+ * pixels directly into the owner's HBM through NVLink/NVSwitch peer stores; no gather, no
+ * de-interleave.  (cudaIpc*; the handle is plain bytes and may be sent over any channel.)            */
+#define RTX_PEER_HANDLE_BYTES 64u
+rtx_status rtx_peer_alloc(int32_t device, uint64_t bytes, void** out_d_ptr);
+rtx_status rtx_peer_free(int32_t device, void* d_ptr);
+rtx_status rtx_peer_export(int32_t device, void* d_ptr, uint8_t* out_handle /* [64] */);
+rtx_status rtx_peer_open(int32_t device, const uint8_t* handle /* [64] */, void** out_d_ptr);
+rtx_status rtx_peer_close(int32_t device, void* d_ptr);
 
 /* ≙ Scene::render_to_image            raytracing/scene.rs:173-178: vertical flip, ×256, saturating
  * `as u8`, no gamma.  out: uint8[height][width][3] (HOST), row 0 = top of the picture.             */

@@ -236,7 +236,7 @@ static rtx_status render_common(rtx_scene* s, uint32_t width, uint32_t height, u
   p.shard_index = sh.index, p.shard_count = sh.count;
   p.tiles_x = (width + TILE - 1) / TILE, p.tiles_y = (height + TILE - 1) / TILE;
   p.my_tiles = (uint32_t)shard_tiles(width, height, sh.index, sh.count);
-  p.compact = sh.count > 1 ? 1u : 0u;
+  p.compact = (sh.count > 1 && !(flags & RTX_FLAG_SHARD_IN_PLACE)) ? 1u : 0u;
   p.work_counter = d_work_counter;
   p.out_rgb = (flags & RTX_FLAG_NO_RADIANCE) ? nullptr : d_rgb;
   p.out_ids = d_ids;
@@ -274,6 +274,41 @@ rtx_status rtx_host_alloc(size_t bytes, void** out) {
   RTX_CUDA_TRY(nullptr, cudaMallocHost(out, bytes ? bytes : 1));
   return RTX_OK;
 }
+// ---- peer frame buffers (cudaIpc) ----------------------------------------------------------------
+rtx_status rtx_peer_alloc(int32_t device, uint64_t bytes, void** out_d_ptr) {
+  if (!out_d_ptr) return fail(nullptr, RTX_ERR_INVALID_ARGUMENT, "null out");
+  RTX_CUDA_TRY(nullptr, cudaSetDevice(device));
+  RTX_CUDA_TRY(nullptr, cudaMalloc(out_d_ptr, bytes ? bytes : 1));
+  return RTX_OK;
+}
+rtx_status rtx_peer_free(int32_t device, void* d_ptr) {
+  RTX_CUDA_TRY(nullptr, cudaSetDevice(device));
+  if (d_ptr) RTX_CUDA_TRY(nullptr, cudaFree(d_ptr));
+  return RTX_OK;
+}
+rtx_status rtx_peer_export(int32_t device, void* d_ptr, uint8_t* out_handle) {
+  static_assert(sizeof(cudaIpcMemHandle_t) == RTX_PEER_HANDLE_BYTES, "handle size");
+  if (!d_ptr || !out_handle) return fail(nullptr, RTX_ERR_INVALID_ARGUMENT, "null argument");
+  RTX_CUDA_TRY(nullptr, cudaSetDevice(device));
+  cudaIpcMemHandle_t h;
+  RTX_CUDA_TRY(nullptr, cudaIpcGetMemHandle(&h, d_ptr));
+  std::memcpy(out_handle, &h, sizeof(h));
+  return RTX_OK;
+}
+rtx_status rtx_peer_open(int32_t device, const uint8_t* handle, void** out_d_ptr) {
+  if (!handle || !out_d_ptr) return fail(nullptr, RTX_ERR_INVALID_ARGUMENT, "null argument");
+  RTX_CUDA_TRY(nullptr, cudaSetDevice(device));
+  cudaIpcMemHandle_t h;
+  std::memcpy(&h, handle, sizeof(h));
+  RTX_CUDA_TRY(nullptr, cudaIpcOpenMemHandle(out_d_ptr, h, cudaIpcMemLazyEnablePeerAccess));
+  return RTX_OK;
+}
+rtx_status rtx_peer_close(int32_t device, void* d_ptr) {
+  RTX_CUDA_TRY(nullptr, cudaSetDevice(device));
+  if (d_ptr) RTX_CUDA_TRY(nullptr, cudaIpcCloseMemHandle(d_ptr));
+  return RTX_OK;
+}
+
 rtx_status rtx_host_free(void* p) {
   if (p) RTX_CUDA_TRY(nullptr, cudaFreeHost(p));
   return RTX_OK;

@@ -142,9 +142,10 @@ RTX_D void consider(Hit& h, double t, uint32_t id, uint32_t ref) {
 // result by nothing.  `disc <= 1e-100` becomes `q <= 1e-100/4`.  h >= 0 gives a negative t, which
 // scene.rs:249 drops; testing it first skips the sqrt + division.
 RTX_D bool sphere_candidate(const double* __restrict__ rec, V3 pos, const RayInv& ri, double* out_h, double* out_q) {
-  const V3 o = pos - mk3(rec[0], rec[1], rec[2]);
+  const double2 cxy = reinterpret_cast<const double2*>(rec)[0], czr = reinterpret_cast<const double2*>(rec)[1];
+  const V3 o = pos - mk3(cxy.x, cxy.y, czr.x);
   const double h = dot(o, ri.dn);
-  const double c = fsub(dot(o, o), rec[3]);
+  const double c = fsub(dot(o, o), czr.y);
   const double q = fsub(fmul(h, h), fmul(ri.a, c));
   *out_h = h;
   *out_q = q;
@@ -211,21 +212,28 @@ RTX_D Hit closest_brute(const SceneView& sc, V3 pos, V3 dir, uint32_t* panics) {
   h.id = MISS_ID;
   h.ref = 0;
   const RayInv ri = ray_invariants(dir);
-  // A sphere that passes the discriminant/sign test still needs a sqrt and a division for its root.  Few
-  // spheres pass per ray, at different loop trips in different lanes, so the root is deferred: a lane keeps
-  // one pending candidate and resolves it when a second one turns up or after the loop — where the lanes
-  // of a warp meet again.  `consider` is a lexicographic (t, id) minimum, so the order is irrelevant.
-  bool pend = false;
-  double pend_h = 0.0, pend_q = 0.0;
-  uint32_t pend_i = 0;
-  for (uint32_t i = 0; i < sc.n_sph; ++i) {
-    double hh, qq;
-    if (sphere_candidate(sc.sph + (size_t)i * SPH_STRIDE, pos, ri, &hh, &qq)) {
-      if (pend) consider(h, sphere_root(pend_h, pend_q, ri), sc.sph_id[pend_i], REF_SPHERE | pend_i);
-      pend = true, pend_h = hh, pend_q = qq, pend_i = i;
+  // Spheres, in chunks of 32: a branch-free pass computes the discriminant/sign test of every sphere in the
+  // chunk and records the survivors as one bit each, so the compiler can overlap the FP64 chains of
+  // neighbouring spheres; the few survivors (usually 0-2 per ray) are then revisited — the same operations
+  // on the same values, so the same bits — for the sqrt + division of the root.  `consider` is a
+  // lexicographic (t, id) minimum, so the visiting order is irrelevant.
+  for (uint32_t base = 0; base < sc.n_sph; base += 32u) {
+    const uint32_t cnt = min(32u, sc.n_sph - base);
+    const double* __restrict__ chunk = sc.sph + (size_t)base * SPH_STRIDE;
+    uint32_t cand = 0u;
+#pragma unroll 2
+    for (uint32_t j = 0; j < cnt; ++j) {
+      double hh, qq;
+      cand |= (sphere_candidate(chunk + (size_t)j * SPH_STRIDE, pos, ri, &hh, &qq) ? 1u : 0u) << j;
+    }
+    while (cand != 0u) {
+      const uint32_t j = (uint32_t)__ffs((int)cand) - 1u;
+      cand &= cand - 1u;
+      double hh, qq;
+      sphere_candidate(chunk + (size_t)j * SPH_STRIDE, pos, ri, &hh, &qq);
+      consider(h, sphere_root(hh, qq, ri), sc.sph_id[base + j], REF_SPHERE | (base + j));
     }
   }
-  if (pend) consider(h, sphere_root(pend_h, pend_q, ri), sc.sph_id[pend_i], REF_SPHERE | pend_i);
   for (uint32_t i = 0; i < sc.n_pl; ++i) {
     double t;
     if (plane_distance(sc.pl + (size_t)i * PL_STRIDE, pos, ri, &t)) consider(h, t, sc.pl_id[i], REF_PLANE | i);

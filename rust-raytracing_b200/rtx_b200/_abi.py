@@ -68,6 +68,8 @@ RTX_ERR_UNSUPPORTED_SHAPE = 4
 RTX_ACCEL_AUTO, RTX_ACCEL_BRUTE, RTX_ACCEL_LBVH = 0, 1, 2
 RTX_FLAG_NO_RADIANCE = 4
 RTX_FLAG_LANE_KERNEL = 8
+RTX_FLAG_SHARD_IN_PLACE = 16
+RTX_PEER_HANDLE_BYTES = 64
 RTX_TILE = 16
 MISS_ID = 0xFFFFFFFF
 
@@ -105,6 +107,11 @@ SIGNATURES = {
     "rtx_device_count": (C.c_int32, []),
     "rtx_host_alloc": (C.c_int32, [C.c_size_t, _P(_vp)]),
     "rtx_host_free": (C.c_int32, [_vp]),
+    "rtx_peer_alloc": (C.c_int32, [C.c_int32, C.c_uint64, _P(_vp)]),
+    "rtx_peer_free": (C.c_int32, [C.c_int32, _vp]),
+    "rtx_peer_export": (C.c_int32, [C.c_int32, _vp, _vp]),
+    "rtx_peer_open": (C.c_int32, [C.c_int32, _vp, _P(_vp)]),
+    "rtx_peer_close": (C.c_int32, [C.c_int32, _vp]),
     "rtx_probe_fp64_peak": (C.c_int32, [C.c_int32, _P(C.c_double), _P(C.c_double)]),
     "rtx_debug_closest_object": (C.c_int32, [_vp, C.c_uint32, _vp, C.c_uint64, _vp, _vp]),
     "rtx_debug_normal_at": (C.c_int32, [_vp, _vp, _vp, C.c_uint64, _vp]),

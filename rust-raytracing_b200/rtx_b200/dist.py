@@ -104,3 +104,102 @@ def render_all_shards_on_one_gpu(scene, width, height, seed, world, flags=RTX_AC
     rgb, ids = deinterleave(width, height, world, g_rgb, g_ids)
     torch.cuda.synchronize(dev)
     return rgb, ids, int(counters[0].item())
+
+
+# ---------------------------------------------------------------------------------------------------
+# Fused render + gather over NVLink peer stores
+# ---------------------------------------------------------------------------------------------------
+class _DevArray:
+    """Raw device memory exposed to torch through __cuda_array_interface__ (no copy)."""
+
+    def __init__(self, ptr, shape, typestr):
+        self.__cuda_array_interface__ = {"shape": tuple(shape), "typestr": typestr, "data": (int(ptr), False),
+                                         "version": 3, "strides": None}
+
+
+class PeerFrame:
+    """The full frame [h][w][3] f64 (+ [h][w] u32 ids) lives in rank `dst`'s HBM; every other rank maps it
+    (rtx_peer_export / rtx_peer_open — cudaIpc) and its render kernel stores finished pixels at their final
+    position through NVLink while it renders (RTX_FLAG_SHARD_IN_PLACE).  ≙ the row-ordered join of
+    scene.rs:167-169 without a gather step: the only collective left is the completion barrier."""
+
+    def __init__(self, width, height, device, group=None, dst=0, want_ids=True):
+        self.width, self.height, self.device, self.group, self.dst = width, height, int(device), group, dst
+        self.world, self.rank = dist.get_world_size(group), dist.get_rank(group)
+        self.want_ids = want_ids
+        lib = _abi.load()
+        self.rgb_bytes = width * height * 24
+        self.ids_off = (self.rgb_bytes + 255) & ~255
+        total = self.ids_off + (width * height * 4 if want_ids else 0)
+        self.owner = self.rank == dst
+        ptr = C.c_void_p()
+        handle = torch.zeros(_abi.RTX_PEER_HANDLE_BYTES, dtype=torch.uint8)
+        if self.owner:
+            _abi.check(lib.rtx_peer_alloc(self.device, total, C.byref(ptr)))
+            buf = (C.c_uint8 * _abi.RTX_PEER_HANDLE_BYTES)()
+            _abi.check(lib.rtx_peer_export(self.device, ptr, buf))
+            handle = torch.frombuffer(bytearray(buf), dtype=torch.uint8).clone()
+        if self.world > 1:
+            backend = dist.get_backend(group)
+            h = handle.to(torch.device("cuda", self.device)) if backend == "nccl" else handle
+            dist.broadcast(h, src=dist.get_global_rank(group, dst) if group is not None else dst, group=group)
+            handle = h.cpu()
+        if not self.owner:
+            raw = (C.c_uint8 * _abi.RTX_PEER_HANDLE_BYTES).from_buffer_copy(bytes(handle.numpy().tobytes()))
+            _abi.check(lib.rtx_peer_open(self.device, raw, C.byref(ptr)))
+        self.ptr = int(ptr.value)
+        self._token = torch.zeros(1, dtype=torch.int32, device=torch.device("cuda", self.device))
+
+    @property
+    def rgb_ptr(self):
+        return self.ptr
+
+    @property
+    def ids_ptr(self):
+        return self.ptr + self.ids_off if self.want_ids else None
+
+    def tensors(self):
+        """torch views of the frame (valid on the owner; on peers they alias remote memory — do not read)."""
+        dev = torch.device("cuda", self.device)
+        rgb = torch.as_tensor(_DevArray(self.ptr, (self.height, self.width, 3), "<f8"), device=dev)
+        ids = torch.as_tensor(_DevArray(self.ptr + self.ids_off, (self.height, self.width), "<i4"),
+                              device=dev) if self.want_ids else None
+        return rgb, ids
+
+    def render(self, scene, seed, counters=None, flags=RTX_ACCEL_AUTO, stream=None):
+        """Every rank renders its tiles straight into the owner's frame, then a stream-ordered barrier:
+        when it completes on the owner's stream every peer's kernel has finished, and a finished kernel's
+        stores are visible system-wide."""
+        if stream is None:
+            stream = torch.cuda.current_stream(torch.device("cuda", self.device)).cuda_stream
+        scene.render_device(self.width, self.height, seed, flags | _abi.RTX_FLAG_SHARD_IN_PLACE,
+                            (self.rank, self.world), self.rgb_ptr, self.ids_ptr,
+                            counters.data_ptr() if counters is not None else None, stream)
+        if self.world > 1:
+            dist.all_reduce(self._token, group=self.group)
+
+    def close(self):
+        lib = _abi.load()
+        if self.ptr:
+            torch.cuda.synchronize(self.device)
+            if self.world > 1:
+                dist.barrier(group=self.group)
+            if self.owner:
+                _abi.check(lib.rtx_peer_free(self.device, C.c_void_p(self.ptr)))
+            else:
+                _abi.check(lib.rtx_peer_close(self.device, C.c_void_p(self.ptr)))
+            self.ptr = 0
+
+
+def render_distributed_p2p(scene, width, height, seed, group=None, flags=RTX_ACCEL_AUTO, want_ids=True, frame=None):
+    """Multi-GPU render with the gather fused into the render kernel (PeerFrame).  Returns
+    (rgb, ids, counters, frame) — rgb/ids are views of the owner's frame on rank 0, None elsewhere."""
+    dev = torch.device("cuda", scene.device)
+    counters = torch.zeros(8, dtype=torch.int64, device=dev)
+    if frame is None:
+        frame = PeerFrame(width, height, scene.device, group, 0, want_ids)
+    frame.render(scene, seed, counters, flags)
+    if frame.owner:
+        rgb, ids = frame.tensors()
+        return rgb, ids, counters, frame
+    return None, None, counters, frame

@@ -45,8 +45,15 @@ pub const RTX_OK: rtx_status = 0;
 pub const RTX_ACCEL_AUTO: u32 = 0;
 pub const RTX_FLAG_NO_RADIANCE: u32 = 4;
 pub const RTX_FLAG_LANE_KERNEL: u32 = 8;
+pub const RTX_FLAG_SHARD_IN_PLACE: u32 = 16;
+pub const RTX_PEER_HANDLE_BYTES: usize = 64;
 
 extern "C" {
+    pub fn rtx_peer_alloc(device: i32, bytes: u64, out_d_ptr: *mut *mut c_void) -> rtx_status;
+    pub fn rtx_peer_free(device: i32, d_ptr: *mut c_void) -> rtx_status;
+    pub fn rtx_peer_export(device: i32, d_ptr: *mut c_void, out_handle: *mut u8) -> rtx_status;
+    pub fn rtx_peer_open(device: i32, handle: *const u8, out_d_ptr: *mut *mut c_void) -> rtx_status;
+    pub fn rtx_peer_close(device: i32, d_ptr: *mut c_void) -> rtx_status;
     pub fn rtx_camera_new(position: *const rtx_vec3, direction: *const rtx_vec3, fov: f64, out: *mut rtx_camera) -> rtx_status;
     pub fn rtx_camera_set_direction(camera: *mut rtx_camera, direction: *const rtx_vec3) -> rtx_status;
     pub fn rtx_config_default(out: *mut rtx_config) -> rtx_status;

@@ -27,14 +27,22 @@ def _worker(rank, world, port, w, h, q):
         rgb, ids, counters = rdist.render_distributed(sc, w, h, seed=3)
         total = counters.clone()
         dist.all_reduce(total)
+        # the same image again, gather fused into the render kernel: peers store into rank 0's frame (NVLink)
+        rgb2, ids2, counters2, frame = rdist.render_distributed_p2p(sc, w, h, seed=3)
+        total2 = counters2.clone()
+        dist.all_reduce(total2)
         torch.cuda.synchronize()
         if rank == 0:
             full, ids_full = sc.render(w, h, seed=3, want_ids=True)
             ok = rgb.cpu().numpy().tobytes() == full.tobytes()
             ok = ok and np.array_equal(ids.cpu().numpy().view(np.uint32), ids_full)
             ok = ok and int(total[0].item()) == sc.last_stats.rays
-            q.put(bool(ok))
+            ok2 = rgb2.cpu().numpy().tobytes() == full.tobytes()
+            ok2 = ok2 and np.array_equal(ids2.cpu().numpy().view(np.uint32), ids_full)
+            ok2 = ok2 and int(total2[0].item()) == sc.last_stats.rays
+            q.put((bool(ok), bool(ok2)))
         dist.barrier()
+        frame.close()
     finally:
         dist.destroy_process_group()
 
@@ -55,4 +63,4 @@ def test_two_gpu_render_equals_one_gpu(rtx, gpu):
     for p in procs:
         p.join(300)
         assert p.exitcode == 0
-    assert q.get(timeout=5) is True
+    assert q.get(timeout=5) == (True, True)  # (NCCL gather path, fused peer-store path)
