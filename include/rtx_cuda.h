@@ -72,6 +72,11 @@ enum {
   RTX_FLAG_NO_RADIANCE = 4u,      /* hit-ID-only render (out_rgb may be NULL)                        */
   RTX_FLAG_LANE_KERNEL = 8u,      /* force the one-pixel-per-lane kernel where the context-pool kernel
                                      would run (same image; for A/B tests and measurements)            */
+  RTX_FLAG_PIXEL_QUEUE = 32u,     /* context-pool kernel: force whole-pixel queue entries (a context runs all
+                                     samples of its pixel)                                             */
+  RTX_FLAG_SAMPLE_QUEUE = 64u,    /* context-pool kernel: force (pixel, sample) queue entries + ordered sum
+                                     pass (short tail: small images, multi-GPU shards).  Default: chosen
+                                     from pixels per resident context.  Same image either way.         */
   RTX_FLAG_SHARD_IN_PLACE = 16u   /* with shard->count > 1: write this shard's pixels at their final
                                      position of the FULL image layout instead of a compact buffer.
                                      d_out_* may then be another GPU's memory (rtx_peer_open): every

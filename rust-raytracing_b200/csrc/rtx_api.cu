@@ -229,6 +229,7 @@ static rtx_status render_common(rtx_scene* s, uint32_t width, uint32_t height, u
   p.layout = s->layout;
   p.use_bvh = use_bvh ? 1u : 0u;
   p.lane_kernel = (flags & RTX_FLAG_LANE_KERNEL) ? 1u : 0u;
+  p.queue_mode = (flags & RTX_FLAG_PIXEL_QUEUE) ? 1u : ((flags & RTX_FLAG_SAMPLE_QUEUE) ? 2u : 0u);
   for (int k = 0; k < 4; ++k) {
     p.bvh.nodes[k] = use_bvh ? s->d_bvh[k] : nullptr;
     p.bvh.root[k] = use_bvh ? s->bvh_root[k] : BVH_END;
@@ -242,6 +243,14 @@ static rtx_status render_common(rtx_scene* s, uint32_t width, uint32_t height, u
   p.out_ids = d_ids;
   p.ray_counter = d_counters;
   if (p.my_tiles == 0) return RTX_OK;
+  p.tail_first = p.my_tiles * GRANS_PER_TILE, p.tail_granules = 0, p.tail_scratch = nullptr, p.tail_done = nullptr;
+  if (!p.lane_kernel && pool_kernel_eligible(p)) {
+    const size_t need = pool_plan_tail(p, s->sm_count);
+    if (need) {
+      RTX_CUDA_TRY(s, grow(&s->d_tail, &s->d_tail_cap, need));
+      p.tail_scratch = s->d_tail;
+    }
+  }
   cudaError_t e = launch_render(p, s->sm_count, stream, launches);
   if (e != cudaSuccess) return cuda_fail(s, e, "render kernel launch");
   return RTX_OK;
@@ -403,6 +412,7 @@ rtx_status rtx_scene_destroy(rtx_scene* s) {
   free_lbvh(s);
   cudaFree(s->d_blob);
   cudaFree(s->d_tables);
+  cudaFree(s->d_tail);
   cudaFree(s->d_work_counter);
   cudaFree(s->d_counters);
   cudaFree(s->d_rgb);

@@ -44,6 +44,8 @@ struct rtx_scene {
   double tab_fov = 0.0;
   bool tab_valid = false;
 
+  double* d_tail = nullptr;  // per-sample radiance of the sample-granular end of the pool kernel's queue
+  size_t d_tail_cap = 0;
   uint32_t* d_work_counter = nullptr;
   unsigned long long* d_counters = nullptr;  // [0] rays [1] paths [2] panics
 
@@ -69,6 +71,8 @@ rtx_status ensure_tables(rtx_scene* s, uint32_t width, uint32_t height, cudaStre
 cudaError_t launch_render(const RenderParams& p, int sm_count, cudaStream_t stream, uint32_t* out_launches);
 // rtx_render_pool.cu: the context-pool kernel for scanned, shared-memory-resident scenes
 bool pool_kernel_eligible(const RenderParams& p);
+// Fills p.tail_first / p.tail_granules; returns the bytes p.tail_scratch must hold (0 = no tail region).
+size_t pool_plan_tail(RenderParams& p, int sm_count);
 cudaError_t launch_render_pool(const RenderParams& p, int sm_count, cudaStream_t stream, uint32_t* out_launches);
 // Builds the LBVH trees if the object list changed since the last build.  Synchronous.
 rtx_status ensure_lbvh(rtx_scene* s, cudaStream_t stream);

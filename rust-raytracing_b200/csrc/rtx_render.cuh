@@ -33,6 +33,7 @@ struct RenderParams {
   BvhView bvh;       // used when use_bvh != 0
   uint32_t use_bvh;
   uint32_t lane_kernel;  // RTX_FLAG_LANE_KERNEL: never pick the context-pool kernel
+  uint32_t queue_mode;   // 0 auto, 1 RTX_FLAG_PIXEL_QUEUE, 2 RTX_FLAG_SAMPLE_QUEUE
   // image shard
   uint32_t shard_index, shard_count;
   uint32_t tiles_x, tiles_y;
@@ -42,10 +43,46 @@ struct RenderParams {
   // outputs
   double* out_rgb;                  // may be null (RTX_FLAG_NO_RADIANCE)
   uint32_t* out_ids;                // may be null
+  // Sample queue (rtx_render_pool.cu, SAMPLE_QUEUE): when tail_granules != 0 (then tail_first == 0 and
+  // tail_granules == all granules of the shard) the work queue hands out (granule, sample) pairs — one sample
+  // per context — and per-sample radiance goes to tail_scratch[((g * rpp + s) * 32 + k) * 3 ..], which
+  // tail_sum_kernel adds up per pixel in sample order (the reference's left fold).
+  uint32_t tail_first, tail_granules;
+  double* tail_scratch;
+  uint32_t* tail_done;  // unused
   unsigned long long* ray_counter;  // [0] rays, [1] paths, [2] triangle panics, [3] hits, [4] nodes visited, [5] prims tested; may be null
 };
 
 #if defined(__CUDACC__)
+// ---- work-queue granule → pixels ---------------------------------------------------------------
+struct Granule {
+  uint32_t x0, y0, w, npix, base_out, tx0, ty0;
+};
+// gidx = index of the granule within this shard's tile list (local tile = gidx / GRANS_PER_TILE).
+__device__ __forceinline__ Granule decode_granule(const RenderParams& p, uint32_t gidx) {
+  Granule g;
+  const uint32_t ltile = gidx / GRANS_PER_TILE, sub = gidx % GRANS_PER_TILE;
+  const uint32_t gtile = ltile * p.shard_count + p.shard_index;
+  const uint32_t ty = gtile / p.tiles_x, tx = gtile % p.tiles_x;
+  g.tx0 = tx * TILE;
+  g.ty0 = ty * TILE;
+  g.x0 = g.tx0 + (sub % (TILE / GRAN_W)) * GRAN_W;
+  g.y0 = g.ty0 + (sub / (TILE / GRAN_W)) * GRAN_H;
+  const uint32_t gw = g.x0 < p.width ? min(GRAN_W, p.width - g.x0) : 0u;
+  const uint32_t gh = g.y0 < p.height ? min(GRAN_H, p.height - g.y0) : 0u;
+  g.w = gw;
+  g.npix = gw * gh;
+  g.base_out = ltile * (TILE * TILE);
+  return g;
+}
+// pixel k (row-major inside the granule) → image pixel index and output index
+__device__ __forceinline__ void granule_pixel(const RenderParams& p, const Granule& g, uint32_t k, uint32_t* x, uint32_t* y,
+                                              uint32_t* out_index) {
+  *x = g.x0 + k % g.w;
+  *y = g.y0 + k / g.w;
+  *out_index = p.compact ? g.base_out + (*y - g.ty0) * TILE + (*x - g.tx0) : *y * p.width + *x;
+}
+
 // ---- TMA bulk copy (global → shared) with an mbarrier ------------------------------------------
 __device__ __forceinline__ uint32_t smem_u32(const void* p) {
   return (uint32_t)__cvta_generic_to_shared(p);

@@ -20,6 +20,8 @@
 #include <cuda_runtime.h>
 #include <math_constants.h>
 
+#include <cstdlib>
+
 #include "rtx_render.cuh"
 #include "rtx_trace.cuh"
 
@@ -27,7 +29,7 @@ namespace rtx {
 
 constexpr int POOL_WARPS = 8;    // warps per CTA
 constexpr int POOL_BLOCK = POOL_WARPS * 32;
-constexpr int POOL_SLOTS = 64;   // pixel contexts per warp (one bit each in a 64-bit state mask)
+constexpr int POOL_SLOTS_MAX = 64;  // pixel contexts per warp (one bit each in a 64-bit state mask)
 constexpr uint32_t FULLMASK = 0xFFFFFFFFu;
 constexpr uint32_t NO_PIXEL = 0xFFFFFFFFu;
 
@@ -43,11 +45,12 @@ enum : int {
   F_M0 = 19,     // 1  sample index | segment << 32
   F_M1 = 20,     // 1  out_index | hit ref << 32
   F_M2 = 21,     // 1  pixel index (NO_PIXEL = none) | hit object id << 32
-  F_COUNT = 22
+  F_M3 = 22,     // 1  SAMPLE_QUEUE: tail_scratch slot of this context's (pixel, sample)
+  F_COUNT = 23
 };
-constexpr size_t POOL_BYTES_PER_WARP = (size_t)F_COUNT * POOL_SLOTS * 8;
-
+template <int POOL_SLOTS>
 struct Pool {
+  static constexpr size_t BYTES_PER_WARP = (size_t)F_COUNT * POOL_SLOTS * 8;
   unsigned long long* w;  // this warp's fields
   __device__ __forceinline__ double ld(int f, uint32_t s) const { return __longlong_as_double((long long)w[f * POOL_SLOTS + s]); }
   __device__ __forceinline__ void st(int f, uint32_t s, double v) { w[f * POOL_SLOTS + s] = (unsigned long long)__double_as_longlong(v); }
@@ -65,7 +68,30 @@ __device__ __forceinline__ unsigned long long warp_or_bit(bool on, uint32_t slot
   return pack2(__reduce_or_sync(FULLMASK, lo), __reduce_or_sync(FULLMASK, hi));
 }
 
-__global__ void __launch_bounds__(POOL_BLOCK, 2) render_pool_kernel(const __grid_constant__ RenderParams p) {
+// Ordered sum after a SAMPLE_QUEUE render: one thread per pixel adds its rpp per-sample radiances in sample
+// order — the reference's left fold from zeros (iter_ops.rs:4-8) — then avg's division (scene.rs:253-259).
+__global__ void __launch_bounds__(256) tail_sum_kernel(const __grid_constant__ RenderParams p) {
+  const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+  const uint32_t tg = t / GRAN_PIXELS, k = t % GRAN_PIXELS;
+  if (tg >= p.tail_granules) return;
+  const Granule g = decode_granule(p, p.tail_first + tg);
+  if (k >= g.npix) return;
+  uint32_t x, y, out_index;
+  granule_pixel(p, g, k, &x, &y, &out_index);
+  const uint32_t rpp = (uint32_t)p.rays_per_pixel;
+  V3 acc = mk3(0.0, 0.0, 0.0);
+  const double* src = p.tail_scratch + ((size_t)tg * rpp * GRAN_PIXELS + k) * 3;
+#pragma unroll 4
+  for (uint32_t s = 0; s < rpp; ++s, src += GRAN_PIXELS * 3) acc = acc + mk3(__ldcs(src), __ldcs(src + 1), __ldcs(src + 2));
+  const V3 px = acc / (double)rpp;
+  p.out_rgb[(size_t)out_index * 3 + 0] = px.x;
+  p.out_rgb[(size_t)out_index * 3 + 1] = px.y;
+  p.out_rgb[(size_t)out_index * 3 + 2] = px.z;
+}
+
+template <int POOL_SLOTS, int MIN_BLOCKS, bool SAMPLE_QUEUE>
+__global__ void __launch_bounds__(POOL_BLOCK, MIN_BLOCKS) render_pool_kernel(const __grid_constant__ RenderParams p) {
+  constexpr size_t POOL_BYTES_PER_WARP = Pool<POOL_SLOTS>::BYTES_PER_WARP;
   extern __shared__ __align__(128) unsigned char smem_raw[];
   // [0,128) mbarrier | scene blob | (128-aligned) POOL_WARPS pools | POOL_WARPS x 64-byte index scratch
   uint64_t* mbar = reinterpret_cast<uint64_t*>(smem_raw);
@@ -76,25 +102,30 @@ __global__ void __launch_bounds__(POOL_BLOCK, 2) render_pool_kernel(const __grid
 
   const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
   const uint32_t lt_mask = (1u << lane) - 1u;
-  Pool P;
+  Pool<POOL_SLOTS> P;
   P.w = reinterpret_cast<unsigned long long*>(smem_raw + pools_off + warp * POOL_BYTES_PER_WARP);
-  unsigned char* idx = smem_raw + pools_off + POOL_WARPS * POOL_BYTES_PER_WARP + warp * POOL_SLOTS;
+  unsigned char* idx = smem_raw + pools_off + POOL_WARPS * POOL_BYTES_PER_WARP + warp * POOL_SLOTS_MAX;
 
   const V3 cam_pos = mk3(p.cam_pos[0], p.cam_pos[1], p.cam_pos[2]);
   const uint32_t rpp = (uint32_t)p.rays_per_pixel;
   const uint32_t max_segments = (uint32_t)p.max_bounces + 1u;  // scene.rs:227
-  const uint32_t total_work = p.my_tiles * GRANS_PER_TILE;
+  const uint32_t total_work = p.tail_first + p.tail_granules * rpp;
 
   // every context starts without a pixel, in REGEN
   P.stu(F_M2, lane, pack2(NO_PIXEL, 0));
-  P.stu(F_M2, lane + 32u, pack2(NO_PIXEL, 0));
   P.stu(F_M0, lane, 0);
-  P.stu(F_M0, lane + 32u, 0);
+  if (lane + 32u < (uint32_t)POOL_SLOTS) {
+    P.stu(F_M2, lane + 32u, pack2(NO_PIXEL, 0));
+    P.stu(F_M0, lane + 32u, 0);
+  }
   __syncwarp();
-  unsigned long long m_regen = ~0ull, m_trace = 0ull, m_shade = 0ull;
+  unsigned long long m_regen = POOL_SLOTS == 64 ? ~0ull : ((1ull << (POOL_SLOTS & 63)) - 1ull), m_trace = 0ull, m_shade = 0ull;
 
   // warp-uniform work-queue state (granule = 8x4 pixels of a 16x16 tile, as in render_megakernel)
-  uint32_t g_x0 = 0, g_y0 = 0, g_w = 0, g_npix = 0, g_next = 0, g_base_out = 0, g_tx0 = 0, g_ty0 = 0;
+  Granule g;
+  g.x0 = g.y0 = g.w = g.npix = g.base_out = g.tx0 = g.ty0 = 0;
+  uint32_t g_next = 0, g_sample = 0, g_slot_base = 0;
+  bool g_single = false;
   bool exhausted = false;
   uint32_t n_rays = 0, n_paths = 0, n_panics = 0, n_hits = 0;
 
@@ -168,8 +199,16 @@ __global__ void __launch_bounds__(POOL_BLOCK, 2) render_pool_kernel(const __grid
           }
         }
         if (end) {
-          P.st3(F_ACC, slot, P.ld3(F_ACC, slot) + res);  // Sum: a + b, left to right
-          P.stu(F_M0, slot, pack2(sample + 1u, 0u));
+          if (SAMPLE_QUEUE) {
+            // single-sample context: this sample's radiance goes to the scratch, the context is free again
+            double* dst = p.tail_scratch + (size_t)(uint32_t)P.ldu(F_M3, slot) * 3;
+            dst[0] = res.x, dst[1] = res.y, dst[2] = res.z;
+            P.stu(F_M2, slot, pack2(NO_PIXEL, 0));
+            P.stu(F_M0, slot, 0);
+          } else {
+            P.st3(F_ACC, slot, P.ld3(F_ACC, slot) + res);  // Sum: a + b, left to right
+            P.stu(F_M0, slot, pack2(sample + 1u, 0u));
+          }
         }
       }
       const unsigned long long to_s = warp_or_bit(to_shade, slot);
@@ -213,7 +252,7 @@ __global__ void __launch_bounds__(POOL_BLOCK, 2) render_pool_kernel(const __grid
       bool need = has && pix == NO_PIXEL;
       uint32_t need_m = __ballot_sync(FULLMASK, need);
       while (need_m != 0u && !exhausted) {
-        if (g_next >= g_npix) {
+        if (g_next >= g.npix) {
           uint32_t w = 0;
           if (lane == 0) w = atomicAdd(p.work_counter, 1u);
           w = __shfl_sync(FULLMASK, w, 0);
@@ -221,27 +260,26 @@ __global__ void __launch_bounds__(POOL_BLOCK, 2) render_pool_kernel(const __grid
             exhausted = true;
             break;
           }
-          const uint32_t ltile = w / GRANS_PER_TILE, sub = w % GRANS_PER_TILE;
-          const uint32_t gtile = ltile * p.shard_count + p.shard_index;
-          const uint32_t ty = gtile / p.tiles_x, tx = gtile % p.tiles_x;
-          g_tx0 = tx * TILE;
-          g_ty0 = ty * TILE;
-          g_x0 = g_tx0 + (sub % (TILE / GRAN_W)) * GRAN_W;
-          g_y0 = g_ty0 + (sub / (TILE / GRAN_W)) * GRAN_H;
-          const uint32_t gw = g_x0 < p.width ? min(GRAN_W, p.width - g_x0) : 0u;
-          const uint32_t gh = g_y0 < p.height ? min(GRAN_H, p.height - g_y0) : 0u;
-          g_w = gw;
-          g_npix = gw * gh;
+          uint32_t gidx = w;
+          g_single = false, g_sample = 0, g_slot_base = 0;
+          if (SAMPLE_QUEUE) {  // a (granule, sample) entry: one sample per context
+            const uint32_t v = w - p.tail_first, tg = v / rpp;
+            g_sample = v - tg * rpp;
+            gidx = p.tail_first + tg;
+            g_single = true;
+            g_slot_base = (tg * rpp + g_sample) * GRAN_PIXELS;
+          }
+          g = decode_granule(p, gidx);
           g_next = 0;
-          g_base_out = ltile * (TILE * TILE);
           continue;  // re-check (the granule may be empty at the image border)
         }
         const uint32_t k = g_next + __popc(need_m & lt_mask);
-        if (need && k < g_npix) {
-          const uint32_t x = g_x0 + k % g_w, y = g_y0 + k / g_w;
+        if (need && k < g.npix) {
+          uint32_t x, y;
+          granule_pixel(p, g, k, &x, &y, &out_index);
           pix = y * p.width + x;
-          out_index = p.compact ? g_base_out + (y - g_ty0) * TILE + (x - g_tx0) : pix;
-          sample = 0;
+          sample = g_sample;
+          if (SAMPLE_QUEUE) P.stu(F_M3, slot, pack2(g_slot_base + k, 0u));
           // scene.rs:213-222 with the libm calls hoisted to the host tables; camera.rs:65-67; scene.rs:203
           M3 to_world;
           to_world.x = mk3(p.to_world[0], p.to_world[1], p.to_world[2]);
@@ -251,7 +289,7 @@ __global__ void __launch_bounds__(POOL_BLOCK, 2) render_pool_kernel(const __grid
           const V3 pix_dir = matvec(to_world, cam_dir);
           P.st3(F_FOCAL, slot, cam_pos + pix_dir * p.focal_length);
           P.st3(F_ACC, slot, mk3(0.0, 0.0, 0.0));  // iter_ops.rs:4-8: the fold starts from zeros()
-          if (p.out_ids) p.out_ids[out_index] = MISS_ID;
+          if (p.out_ids && g_sample == 0) p.out_ids[out_index] = MISS_ID;
           need = false;
           if (rpp == 0) {  // avg of an empty iterator: zeros / 0.0 = NaN (scene.rs:253-259)
             if (p.out_rgb) {
@@ -264,7 +302,7 @@ __global__ void __launch_bounds__(POOL_BLOCK, 2) render_pool_kernel(const __grid
             need = true;
           }
         }
-        g_next = min(g_next + (uint32_t)__popc(need_m), g_npix);
+        g_next = min(g_next + (uint32_t)__popc(need_m), g.npix);
         need_m = __ballot_sync(FULLMASK, need);
       }
       const bool go = has && pix != NO_PIXEL;
@@ -317,22 +355,67 @@ bool pool_kernel_eligible(const RenderParams& p) {
          p.max_bounces < 0x7FFFFFFEull;
 }
 
-cudaError_t launch_render_pool(const RenderParams& p, int sm_count, cudaStream_t stream, uint32_t* out_launches) {
+// Which queue this launch uses.  With whole-pixel entries a context runs its pixel's rpp samples one after
+// the other, so the kernel cannot end before the most expensive pixel handed out last has finished:
+// rpp x (up to max_bounces + 1) segments of latency — on S1 at 64 spp more than a millisecond of under-filled
+// machine per launch whatever the shard size, which is what limits strong scaling.  The SAMPLE_QUEUE hands
+// out (granule, sample) entries instead: the tail is one path, at the price of 24 B of scratch per path and
+// the ordered sum afterwards.  Chosen when rpp >= 4 and the scratch fits the budget
+// (RTX_FLAG_PIXEL_QUEUE / RTX_FLAG_SAMPLE_QUEUE force one or the other).
+// Returns the scratch bytes needed (0 = whole-pixel queue): [granules * rpp * 32 * 3] f64.
+size_t pool_plan_tail(RenderParams& p, int sm_count) {
+  const uint64_t granules = (uint64_t)p.my_tiles * GRANS_PER_TILE;
+  p.tail_first = (uint32_t)granules;
+  p.tail_granules = 0;
+  p.tail_scratch = nullptr;
+  p.tail_done = nullptr;
+  const int force = p.queue_mode == 1 ? 0 : (p.queue_mode == 2 ? 1 : -1);
+  const uint64_t rpp = p.rays_per_pixel;
+  if (force == 0 || !p.out_rgb || rpp < 1 || rpp > 65536) return 0;
+  if (force != 1 && rpp < 4) return 0;
+  // Whole-pixel entries are ~4 % faster in the steady state (no scratch, no sum pass): keep them when every
+  // resident context gets many pixels, so the tail is a small share (measured cross-over: N = 1 at 1080p,
+  // 13.7 pixels per context, 12.32 vs 12.77 ms; N = 2, 6.8 per context, 6.72 vs 6.41 ms).
+  const uint64_t contexts = (uint64_t)sm_count * 2 * POOL_WARPS * POOL_SLOTS_MAX;
+  if (force != 1 && granules * GRAN_PIXELS >= 10 * contexts) return 0;
+  const uint64_t cap_bytes = 4ull << 30;  // scratch budget
+  const uint64_t bytes = granules * rpp * GRAN_PIXELS * 24;
+  if (bytes > cap_bytes || granules * rpp * GRAN_PIXELS > 0xFFFFFFFFull) return 0;
+  p.tail_granules = (uint32_t)granules;
+  p.tail_first = 0;
+  return (size_t)bytes;
+}
+
+template <int POOL_SLOTS, int MIN_BLOCKS, bool SAMPLE_QUEUE>
+static cudaError_t launch_pool_variant(const RenderParams& p, int sm_count, cudaStream_t stream, uint32_t* out_launches) {
   const size_t pools_off = (128u + (size_t)p.layout.bytes + 127u) & ~(size_t)127u;
-  const size_t smem = pools_off + POOL_WARPS * POOL_BYTES_PER_WARP + POOL_WARPS * POOL_SLOTS;
+  const size_t smem = pools_off + POOL_WARPS * Pool<POOL_SLOTS>::BYTES_PER_WARP + POOL_WARPS * POOL_SLOTS_MAX;
   cudaError_t e = cudaMemsetAsync(p.work_counter, 0, sizeof(uint32_t), stream);
   if (e != cudaSuccess) return e;
-  const uint64_t total_work = (uint64_t)p.my_tiles * GRANS_PER_TILE;
-  // persistent grid: 2 CTAs per SM, never more contexts than pixels
-  const uint64_t per_block = (uint64_t)POOL_WARPS * POOL_SLOTS / GRAN_PIXELS;  // granules one CTA can hold at once
+  const uint64_t total_work = (uint64_t)p.tail_first + (uint64_t)p.tail_granules * p.rays_per_pixel;
+  // persistent grid: MIN_BLOCKS CTAs per SM, never more contexts than queue entries can feed
+  const uint64_t per_block = (uint64_t)POOL_WARPS * POOL_SLOTS / GRAN_PIXELS;  // queue entries one CTA can hold at once
   uint64_t want_blocks = (total_work + per_block - 1) / per_block;
-  uint64_t grid = (uint64_t)sm_count * 2;
+  uint64_t grid = (uint64_t)sm_count * MIN_BLOCKS;
   if (want_blocks < grid) grid = want_blocks ? want_blocks : 1;
-  e = cudaFuncSetAttribute(render_pool_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  e = cudaFuncSetAttribute(render_pool_kernel<POOL_SLOTS, MIN_BLOCKS, SAMPLE_QUEUE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return e;
-  render_pool_kernel<<<(unsigned)grid, POOL_BLOCK, smem, stream>>>(p);
+  render_pool_kernel<POOL_SLOTS, MIN_BLOCKS, SAMPLE_QUEUE><<<(unsigned)grid, POOL_BLOCK, smem, stream>>>(p);
+  if (out_launches) *out_launches += 1;
+  e = cudaGetLastError();
+  if (e != cudaSuccess || !SAMPLE_QUEUE) return e;
+  const unsigned threads = p.tail_granules * GRAN_PIXELS;
+  tail_sum_kernel<<<(threads + 255) / 256, 256, 0, stream>>>(p);
   if (out_launches) *out_launches += 1;
   return cudaGetLastError();
+}
+
+cudaError_t launch_render_pool(const RenderParams& p, int sm_count, cudaStream_t stream, uint32_t* out_launches) {
+  // RTX_POOL_VARIANT (measurement knob): 0 = 64 contexts/warp, 2 CTAs/SM; 1 = 48 contexts/warp, 3 CTAs/SM
+  static const int variant = [] { const char* v = getenv("RTX_POOL_VARIANT"); return v ? atoi(v) : 0; }();
+  if (p.tail_granules != 0) return launch_pool_variant<64, 2, true>(p, sm_count, stream, out_launches);
+  if (variant == 1) return launch_pool_variant<48, 3, false>(p, sm_count, stream, out_launches);
+  return launch_pool_variant<64, 2, false>(p, sm_count, stream, out_launches);
 }
 
 }  // namespace rtx

@@ -64,7 +64,7 @@ int main() {
   for (auto& row : img)
     for (auto& p : row) sum += p.x + p.y + p.z;
   EXPECT(std::isfinite(sum) && sum > 0);
-  EXPECT(st.rays > 320 * 200 * 4 && st.paths == 320ull * 200 * 4 && st.kernel_launches == 1);
+  EXPECT(st.rays > 320 * 200 * 4 && st.paths == 320ull * 200 * 4 && st.kernel_launches >= 1 && st.kernel_launches <= 2);
   // top row (y = h-1) looks at the sky: black; bottom row (y = 0) looks at the lit ground
   EXPECT(img[199][160] == Vector3::zeros());
   EXPECT(img[0][160].x > 0);

@@ -69,6 +69,8 @@ RTX_ACCEL_AUTO, RTX_ACCEL_BRUTE, RTX_ACCEL_LBVH = 0, 1, 2
 RTX_FLAG_NO_RADIANCE = 4
 RTX_FLAG_LANE_KERNEL = 8
 RTX_FLAG_SHARD_IN_PLACE = 16
+RTX_FLAG_PIXEL_QUEUE = 32
+RTX_FLAG_SAMPLE_QUEUE = 64
 RTX_PEER_HANDLE_BYTES = 64
 RTX_TILE = 16
 MISS_ID = 0xFFFFFFFF

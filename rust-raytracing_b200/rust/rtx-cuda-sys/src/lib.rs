@@ -46,6 +46,8 @@ pub const RTX_ACCEL_AUTO: u32 = 0;
 pub const RTX_FLAG_NO_RADIANCE: u32 = 4;
 pub const RTX_FLAG_LANE_KERNEL: u32 = 8;
 pub const RTX_FLAG_SHARD_IN_PLACE: u32 = 16;
+pub const RTX_FLAG_PIXEL_QUEUE: u32 = 32;
+pub const RTX_FLAG_SAMPLE_QUEUE: u32 = 64;
 pub const RTX_PEER_HANDLE_BYTES: usize = 64;
 
 extern "C" {

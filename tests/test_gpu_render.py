@@ -187,7 +187,9 @@ def test_context_pool_kernel_equals_lane_kernel(rtx, gpu):
     from rtx_b200 import Camera, Config, Material, Object, Plane, Scene, Sphere, Triangle, scenes
     BR, LANE = rtx.RTX_ACCEL_BRUTE, rtx.RTX_ACCEL_BRUTE | rtx.RTX_FLAG_LANE_KERNEL
     cases = []
-    for spp, depth, w, h in [(4, 8, 333, 77), (1, 0, 17, 5), (3, 2, 1, 1), (0, 8, 40, 30), (16, 8, 256, 144)]:
+    # (4, 8, 640, 360): more pixels than resident contexts, so both ends of the two-granularity queue are used
+    for spp, depth, w, h in [(4, 8, 333, 77), (1, 0, 17, 5), (3, 2, 1, 1), (0, 8, 40, 30), (16, 8, 256, 144),
+                             (4, 8, 640, 360), (5, 3, 700, 301)]:
         cases.append((scenes.sphere_demo(rays_per_pixel=spp, max_bounces=depth), w, h))
     tri = Scene(Config().with_rays_per_pixel(3).with_max_bounces(4), Camera((0, 0, 1), (1, 0, 0.2), 1.2))
     tri.add_object(Object(Triangle([(4, -2, 3), (8, 0, 3.5), (4, 2, 3)]), Material((0.7, 0.7, 0.2), (0, 0, 0), 0.3)))
@@ -203,5 +205,10 @@ def test_context_pool_kernel_equals_lane_kernel(rtx, gpu):
         b, ib = sc.render(w, h, seed=5, flags=LANE, want_ids=True)
         sb = (sc.last_stats.rays, sc.last_stats.paths, sc.last_stats.hits, sc.last_stats.prims_tested)
         assert a.tobytes() == b.tobytes() and np.array_equal(ia, ib) and sa == sb, (w, h, sa, sb)
+        # both queue granularities of the pool kernel: whole pixels per context / one (pixel, sample) per context
+        for q in (rtx.RTX_FLAG_PIXEL_QUEUE, rtx.RTX_FLAG_SAMPLE_QUEUE):
+            c, ic = sc.render(w, h, seed=5, flags=BR | q, want_ids=True)
+            sq = (sc.last_stats.rays, sc.last_stats.paths, sc.last_stats.hits, sc.last_stats.prims_tested)
+            assert c.tobytes() == b.tobytes() and np.array_equal(ic, ib) and sq == sb, (w, h, q, sq, sb)
     a = empty.render(33, 9, seed=1)
     assert not a.any()
