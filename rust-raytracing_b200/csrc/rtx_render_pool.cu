@@ -93,7 +93,8 @@ template <int POOL_SLOTS, int MIN_BLOCKS, bool SAMPLE_QUEUE>
 __global__ void __launch_bounds__(POOL_BLOCK, MIN_BLOCKS) render_pool_kernel(const __grid_constant__ RenderParams p) {
   constexpr size_t POOL_BYTES_PER_WARP = Pool<POOL_SLOTS>::BYTES_PER_WARP;
   extern __shared__ __align__(128) unsigned char smem_raw[];
-  // [0,128) mbarrier | scene blob | (128-aligned) POOL_WARPS pools | POOL_WARPS x 64-byte index scratch
+  // [0,128) mbarrier | scene blob | (128-aligned) POOL_WARPS pools | POOL_WARPS x 64-byte index scratch |
+  // glibc sin/cos table (3520 B)
   uint64_t* mbar = reinterpret_cast<uint64_t*>(smem_raw);
   unsigned char* blob = smem_raw + 128;
   stage_blob(blob, p.scene_blob, p.layout.bytes, mbar);
@@ -105,6 +106,9 @@ __global__ void __launch_bounds__(POOL_BLOCK, MIN_BLOCKS) render_pool_kernel(con
   Pool<POOL_SLOTS> P;
   P.w = reinterpret_cast<unsigned long long*>(smem_raw + pools_off + warp * POOL_BYTES_PER_WARP);
   unsigned char* idx = smem_raw + pools_off + POOL_WARPS * POOL_BYTES_PER_WARP + warp * POOL_SLOTS_MAX;
+  double* sctab = reinterpret_cast<double*>(smem_raw + pools_off + POOL_WARPS * POOL_BYTES_PER_WARP + POOL_WARPS * POOL_SLOTS_MAX);
+  for (uint32_t i = threadIdx.x; i < 440u; i += POOL_BLOCK) sctab[i] = SINCOS_TAB_DEV[i];
+  __syncthreads();
 
   const V3 cam_pos = mk3(p.cam_pos[0], p.cam_pos[1], p.cam_pos[2]);
   const uint32_t rpp = (uint32_t)p.rays_per_pixel;
@@ -225,7 +229,7 @@ __global__ void __launch_bounds__(POOL_BLOCK, MIN_BLOCKS) render_pool_kernel(con
         WyRand rng;
         rng.s = P.ldu(F_RNG, slot);
         const V3 n = normal_at(sc, ref, pos);
-        const V3 nd = random_bounce_dir(rng, dir, n, sc.mat[(size_t)id * MAT_STRIDE + 6]);
+        const V3 nd = random_bounce_dir(rng, dir, n, sc.mat[(size_t)id * MAT_STRIDE + 6], sctab);
         P.st3(F_DIR, slot, nd);
         P.stu(F_RNG, slot, rng.s);
       }
@@ -389,7 +393,7 @@ size_t pool_plan_tail(RenderParams& p, int sm_count) {
 template <int POOL_SLOTS, int MIN_BLOCKS, bool SAMPLE_QUEUE>
 static cudaError_t launch_pool_variant(const RenderParams& p, int sm_count, cudaStream_t stream, uint32_t* out_launches) {
   const size_t pools_off = (128u + (size_t)p.layout.bytes + 127u) & ~(size_t)127u;
-  const size_t smem = pools_off + POOL_WARPS * Pool<POOL_SLOTS>::BYTES_PER_WARP + POOL_WARPS * POOL_SLOTS_MAX;
+  const size_t smem = pools_off + POOL_WARPS * Pool<POOL_SLOTS>::BYTES_PER_WARP + POOL_WARPS * POOL_SLOTS_MAX + 440 * sizeof(double);
   cudaError_t e = cudaMemsetAsync(p.work_counter, 0, sizeof(uint32_t), stream);
   if (e != cudaSuccess) return e;
   const uint64_t total_work = (uint64_t)p.tail_first + (uint64_t)p.tail_granules * p.rays_per_pixel;

@@ -9,6 +9,7 @@
 #endif
 #include "rtx_rng.cuh"
 #include "rtx_scene.cuh"
+#include "rtx_sincos.cuh"
 
 namespace rtx {
 
@@ -268,18 +269,21 @@ RTX_D V3 normal_at(const SceneView& sc, uint32_t ref, V3 pos) {
 }
 
 // math/vector.rs:36-45
-RTX_D V3 random_direction(WyRand& g) {
+RTX_D V3 random_direction(WyRand& g, const double* sctab) {
   const double z = fsub(fmul(wy_f64(g), 2.0), 1.0);
   const double theta = fmul(fmul(wy_f64(g), 2.0), 3.14159265358979323846264338327950288);
   const double r = fsqrt(fsub(1.0, fmul(z, z)));
+  // glibc's sin/cos restated bit for bit (rtx_sincos.cuh): CUDA's sincos() differs from it by an ulp in
+  // ~15 % of the draws, which is enough to flip later hits on triangle scenes.
   double s, c;
-  sincos(theta, &s, &c);  // ≤ 1-2 ulp from glibc's sin/cos: the one non-bit-exact step
+  libm_sincos(theta, sctab, &s, &c);
   return vnorm(mk3(fmul(r, c), fmul(r, s), z));
 }
 
 // scene.rs:279-291
-RTX_D V3 random_bounce_dir(WyRand& g, V3 ray_dir, V3 n, double roughness) {
-  const V3 rd = random_direction(g);
+// sctab: glibc's sin/cos table — sincos_table() (global memory) or a copy staged in shared memory
+RTX_D V3 random_bounce_dir(WyRand& g, V3 ray_dir, V3 n, double roughness, const double* sctab = sincos_table()) {
+  const V3 rd = random_direction(g, sctab);
   const V3 refl = ray_dir - (n * 2.0) * dot(ray_dir, n);
   const V3 to_refl = refl - rd;
   const double mult = fsub(1.0, roughness);
