@@ -161,6 +161,34 @@ rtx_status rtx_deinterleave_tiles(uint32_t width, uint32_t height, uint32_t coun
                                   const void* d_gathered_rgb, void* d_out_rgb,
                                   const void* d_gathered_ids, void* d_out_ids, void* cuda_stream);
 
+/* ---- the reference's f32 wire format (GpuSerialize) ---------------------------------------------
+ * ≙ gpu::Scene::new / add_object (raytracing/gpu/scene.rs:11-25, gpu/gpu_state.rs:31-77): the serialized
+ * camera (camera.rs:70-78), config (scene.rs:67-76), object records (gpu/object.rs:34-42) and per-type shape
+ * buffers (object/sphere.rs:36-42, plane.rs:38-46, triangle.rs:130-136) of a `gpu::Scene` are accepted as they
+ * are; each f32 widens to f64 exactly and the scene is rendered with the CPU path's f64 semantics.
+ * object_type = GpuShape::object_type() of the buffer ("…::sphere", "…::plane", "…::triangle"); a buffer's
+ * position in the array is the shape_id the object records refer to.  The decode functions are pure host
+ * code (no device needed).                                                                          */
+#define RTX_WIRE_CAMERA_BYTES   32u
+#define RTX_WIRE_CONFIG_BYTES   20u
+#define RTX_WIRE_OBJECT_BYTES   48u
+#define RTX_WIRE_SPHERE_BYTES   16u
+#define RTX_WIRE_PLANE_BYTES    32u
+#define RTX_WIRE_TRIANGLE_BYTES 48u
+enum { RTX_WIRE_SPHERE = 0, RTX_WIRE_PLANE = 1, RTX_WIRE_TRIANGLE = 2 };
+typedef struct { const char* object_type; const void* shape_bytes; uint64_t shape_count; } rtx_wire_shape_buffer;
+rtx_status rtx_wire_decode_camera(const void* bytes /* [32] */, rtx_camera* out);
+rtx_status rtx_wire_decode_config(const void* bytes /* [20] */, rtx_config* out);
+/* out_kinds[i] = RTX_WIRE_*; out_shapes[i]: sphere = {vertices[0] = position, vertices[1].x = radius},
+ * plane = {vertices[0] = position, vertices[1] = normal}, triangle = its three vertices.             */
+rtx_status rtx_wire_decode_objects(const void* object_records, uint64_t n_objects,
+                                   const rtx_wire_shape_buffer* shape_buffers, uint32_t n_shape_buffers,
+                                   uint32_t* out_kinds, rtx_triangle* out_shapes, rtx_material* out_materials);
+rtx_status rtx_scene_add_wire_objects(rtx_scene* scene, const void* object_records, uint64_t n_objects,
+                                      const rtx_wire_shape_buffer* shape_buffers, uint32_t n_shape_buffers);
+rtx_status rtx_scene_set_wire_camera(rtx_scene* scene, const void* bytes /* [32] */);
+rtx_status rtx_scene_set_wire_config(rtx_scene* scene, const void* bytes /* [20] */);
+
 /* ---- peer frame buffers (multi-GPU, one process per GPU) ------------------------------------------
  * The owner (rank 0) allocates the frame with rtx_peer_alloc and exports a 64-byte handle; the other
  * processes of the node open it and pass the returned pointer as d_out_rgb / d_out_primary_hit_id of

@@ -289,6 +289,26 @@ class Scene:
         else:
             self._batches.append((kind, shapes, materials))
 
+    def add_wire_objects(self, records, buffers):
+        """≙ gpu::Scene::add_object's serialized state (gpu/gpu_state.rs:53-77): 48-byte object records plus one
+        (object_type tag, bytes, count) shape buffer per shape_id, in the reference's f32 wire format (wire.py)."""
+        from . import wire
+        kinds, shapes, mats = wire.decode_objects(records, buffers)
+        ncol = {SHAPE_SPHERE: 4, SHAPE_PLANE: 6, SHAPE_TRIANGLE: 9}
+        for k, s, m in zip(kinds.tolist(), shapes, mats):
+            self._append(int(k), s[None, :ncol[int(k)]].copy(), m[None, :].copy())
+
+    @classmethod
+    def from_wire(cls, camera_bytes, config_bytes, records, buffers, device=0):
+        """A scene from the byte buffers a reference `gpu::Scene` holds (camera.rs:70-78, scene.rs:67-76, ...)."""
+        from . import wire
+        cc, cf = wire.decode_camera(camera_bytes), wire.decode_config(config_bytes)
+        cam = Camera((cc.position.x, cc.position.y, cc.position.z), (cc.direction.x, cc.direction.y, cc.direction.z), cc.fov)
+        cfg = Config(cf.rays_per_pixel, cf.max_bounces, cf.focal_length, cf.focal_offset, cf.non_focal_offset)
+        sc = cls(cfg, cam, device)
+        sc.add_wire_objects(records, buffers)
+        return sc
+
     @property
     def object_count(self):
         return sum(b[1].shape[0] for b in self._batches)

@@ -52,6 +52,10 @@ class Stats(C.Structure):
                 ("nodes_visited", C.c_uint64), ("prims_tested", C.c_uint64), ("hits", C.c_uint64)]
 
 
+class WireShapeBuffer(C.Structure):  # one per-type shape buffer of gpu_state.rs:53-77
+    _fields_ = [("object_type", C.c_char_p), ("shape_bytes", C.c_void_p), ("shape_count", C.c_uint64)]
+
+
 class Shard(C.Structure):
     _fields_ = [("index", C.c_uint32), ("count", C.c_uint32)]
 
@@ -109,6 +113,12 @@ SIGNATURES = {
     "rtx_device_count": (C.c_int32, []),
     "rtx_host_alloc": (C.c_int32, [C.c_size_t, _P(_vp)]),
     "rtx_host_free": (C.c_int32, [_vp]),
+    "rtx_wire_decode_camera": (C.c_int32, [_vp, _P(CameraC)]),
+    "rtx_wire_decode_config": (C.c_int32, [_vp, _P(ConfigC)]),
+    "rtx_wire_decode_objects": (C.c_int32, [_vp, C.c_uint64, _P(WireShapeBuffer), C.c_uint32, _vp, _vp, _vp]),
+    "rtx_scene_add_wire_objects": (C.c_int32, [_vp, _vp, C.c_uint64, _P(WireShapeBuffer), C.c_uint32]),
+    "rtx_scene_set_wire_camera": (C.c_int32, [_vp, _vp]),
+    "rtx_scene_set_wire_config": (C.c_int32, [_vp, _vp]),
     "rtx_peer_alloc": (C.c_int32, [C.c_int32, C.c_uint64, _P(_vp)]),
     "rtx_peer_free": (C.c_int32, [C.c_int32, _vp]),
     "rtx_peer_export": (C.c_int32, [C.c_int32, _vp, _vp]),
