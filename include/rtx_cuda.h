@@ -131,6 +131,24 @@ rtx_status rtx_scene_add_spheres(rtx_scene* scene, const rtx_sphere* shapes, con
 rtx_status rtx_scene_add_planes(rtx_scene* scene, const rtx_plane* shapes, const rtx_material* materials, uint64_t n);
 rtx_status rtx_scene_add_triangles(rtx_scene* scene, const rtx_triangle* shapes, const rtx_material* materials, uint64_t n);
 rtx_status rtx_scene_clear_objects(rtx_scene* scene);
+/* In-place replacement of existing objects between renders.  ≙ mutating a shape behind its Arc<Mutex<…>>
+ * (raytracing/object.rs:12) / overwriting a record of the wgpu backend's FrequentlyChangedBuffer
+ * (raytracing/gpu/gpu_state/buffer.rs:69-115).  object_indices[i] = global insertion index of an object of the
+ * SAME shape kind; materials may be NULL (keep the old ones).  Only the touched records are re-uploaded, and the
+ * LBVH is REFITTED (same hierarchy, new boxes) instead of rebuilt — results stay identical to the scan because
+ * the tree only culls.  A change that alters tree membership (a primitive becoming non-finite or a triangle
+ * changing its elimination pivots) falls back to a rebuild.  rtx_scene_rebuild_accel forces a rebuild, e.g.
+ * after primitives moved far and the refitted tree has become slow.                                   */
+rtx_status rtx_scene_update_spheres(rtx_scene* scene, const uint64_t* object_indices, const rtx_sphere* shapes,
+                                    const rtx_material* materials, uint64_t n);
+rtx_status rtx_scene_update_planes(rtx_scene* scene, const uint64_t* object_indices, const rtx_plane* shapes,
+                                   const rtx_material* materials, uint64_t n);
+rtx_status rtx_scene_update_triangles(rtx_scene* scene, const uint64_t* object_indices, const rtx_triangle* shapes,
+                                      const rtx_material* materials, uint64_t n);
+rtx_status rtx_scene_rebuild_accel(rtx_scene* scene);
+/* Number of LBVH refits / full builds this scene has performed (statistics; tests). */
+uint32_t   rtx_scene_accel_refits(const rtx_scene* scene);
+uint32_t   rtx_scene_accel_builds(const rtx_scene* scene);
 uint64_t   rtx_scene_object_count(const rtx_scene* scene);
 
 /* ---- render -------------------------------------------------------------------------------- */

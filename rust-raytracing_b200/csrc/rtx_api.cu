@@ -64,8 +64,43 @@ static cudaError_t grow(T** p, size_t* cap, size_t need_bytes) {
 
 static inline uint32_t align16(size_t v) { return (uint32_t)((v + 15) & ~(size_t)15); }
 
+// Re-uploads only the records touched by rtx_scene_update_* (the layout is unchanged): element by element for a
+// few, the whole array of that kind for many.
+template <typename T>
+static cudaError_t upload_touched(unsigned char* d_base, const std::vector<T>& host, size_t stride_elems,
+                                  std::vector<uint32_t>& touched, cudaStream_t stream) {
+  if (touched.empty()) return cudaSuccess;
+  cudaError_t e = cudaSuccess;
+  if (touched.size() > 256) {
+    e = cudaMemcpyAsync(d_base, host.data(), host.size() * sizeof(T), cudaMemcpyHostToDevice, stream);
+  } else {
+    for (uint32_t i : touched) {
+      const size_t o = (size_t)i * stride_elems;
+      e = cudaMemcpyAsync(d_base + o * sizeof(T), host.data() + o, stride_elems * sizeof(T), cudaMemcpyHostToDevice, stream);
+      if (e != cudaSuccess) break;
+    }
+  }
+  touched.clear();
+  return e;
+}
+
 rtx_status ensure_uploaded(rtx_scene* s, cudaStream_t stream) {
-  if (!s->dirty && s->d_blob) return RTX_OK;
+  if (!s->dirty && s->d_blob) {
+    const bool any = !s->upd_sph.empty() || !s->upd_pl.empty() || !s->upd_tri.empty() || !s->upd_mat.empty();
+    if (!any) return RTX_OK;
+    const SceneLayout& L = s->layout;
+    if (s->d_tri_raw && !s->upd_tri.empty()) {  // the LBVH's vertex copy follows the same updates
+      std::vector<uint32_t> t = s->upd_tri;
+      RTX_CUDA_TRY(s, upload_touched(reinterpret_cast<unsigned char*>(s->d_tri_raw), s->tri_raw, 9, t, stream));
+    }
+    RTX_CUDA_TRY(s, upload_touched(s->d_blob + L.off_sph, s->sph, SPH_STRIDE, s->upd_sph, stream));
+    RTX_CUDA_TRY(s, upload_touched(s->d_blob + L.off_pl, s->pl, PL_STRIDE, s->upd_pl, stream));
+    RTX_CUDA_TRY(s, upload_touched(s->d_blob + L.off_tri, s->tri, TRI_STRIDE, s->upd_tri, stream));
+    RTX_CUDA_TRY(s, upload_touched(s->d_blob + L.off_mat, s->mat, MAT_STRIDE, s->upd_mat, stream));
+    RTX_CUDA_TRY(s, cudaStreamSynchronize(stream));  // pageable sources
+    return RTX_OK;
+  }
+  s->upd_sph.clear(), s->upd_pl.clear(), s->upd_tri.clear(), s->upd_mat.clear();
   SceneLayout L{};
   L.n_obj = (uint32_t)s->n_obj;
   L.n_sph = (uint32_t)s->sph_id.size();
@@ -413,6 +448,7 @@ rtx_status rtx_scene_destroy(rtx_scene* s) {
   cudaFree(s->d_blob);
   cudaFree(s->d_tables);
   cudaFree(s->d_tail);
+  cudaFree(s->d_tri_raw);
   cudaFree(s->d_work_counter);
   cudaFree(s->d_counters);
   cudaFree(s->d_rgb);
@@ -470,6 +506,7 @@ rtx_status rtx_scene_add_spheres(rtx_scene* s, const rtx_sphere* shapes, const r
     const size_t o = s->sph.size();
     s->sph.resize(o + SPH_STRIDE);
     pack_sphere(&shapes[i].position.x, shapes[i].radius, &s->sph[o]);
+    s->obj_ref.push_back(REF_SPHERE | (uint32_t)s->sph_id.size());
     s->sph_id.push_back((uint32_t)s->n_obj++);
     push_material(s, materials[i]);
   }
@@ -485,6 +522,7 @@ rtx_status rtx_scene_add_planes(rtx_scene* s, const rtx_plane* shapes, const rtx
     const size_t o = s->pl.size();
     s->pl.resize(o + PL_STRIDE);
     pack_plane(&shapes[i].position.x, &shapes[i].normal.x, &s->pl[o]);
+    s->obj_ref.push_back(REF_PLANE | (uint32_t)s->pl_id.size());
     s->pl_id.push_back((uint32_t)s->n_obj++);
     push_material(s, materials[i]);
   }
@@ -502,6 +540,7 @@ rtx_status rtx_scene_add_triangles(rtx_scene* s, const rtx_triangle* shapes, con
     s->tri.resize(o + TRI_STRIDE);
     pack_triangle(&shapes[i].vertices[0].x, &s->tri[o]);
     s->tri_raw.insert(s->tri_raw.end(), &shapes[i].vertices[0].x, &shapes[i].vertices[0].x + 9);
+    s->obj_ref.push_back(REF_TRIANGLE | (uint32_t)s->tri_id.size());
     s->tri_id.push_back((uint32_t)s->n_obj++);
     push_material(s, materials[i]);
   }
@@ -509,11 +548,88 @@ rtx_status rtx_scene_add_triangles(rtx_scene* s, const rtx_triangle* shapes, con
   s->bvh_valid = false;
   return RTX_OK;
 }
+// ---- in-place updates (N2) -------------------------------------------------------------------------
+static rtx_status check_update(rtx_scene* s, const uint64_t* idx, const void* shapes, uint64_t n, uint32_t kind) {
+  if (!s) return fail(s, RTX_ERR_INVALID_ARGUMENT, "null scene");
+  if (n && (!idx || !shapes)) return fail(s, RTX_ERR_INVALID_ARGUMENT, "null indices/shapes");
+  for (uint64_t i = 0; i < n; ++i) {
+    if (idx[i] >= s->n_obj) return fail(s, RTX_ERR_INVALID_ARGUMENT, "object index out of range");
+    if ((s->obj_ref[idx[i]] & ~REF_INDEX_MASK) != kind)
+      return fail(s, RTX_ERR_INVALID_ARGUMENT, "object is of a different shape kind");
+  }
+  return RTX_OK;
+}
+static void update_material(rtx_scene* s, uint64_t obj, const rtx_material& m) {
+  pack_material(&m.base_color.x, &m.emission_color.x, m.roughness, &s->mat[(size_t)obj * MAT_STRIDE]);
+  s->upd_mat.push_back((uint32_t)obj);
+}
+rtx_status rtx_scene_update_spheres(rtx_scene* s, const uint64_t* idx, const rtx_sphere* shapes, const rtx_material* materials,
+                                    uint64_t n) {
+  if (s == nullptr) return fail(s, RTX_ERR_INVALID_ARGUMENT, "null scene");
+  std::lock_guard<std::mutex> lk(s->mu);
+  rtx_status st = check_update(s, idx, shapes, n, REF_SPHERE);
+  if (st != RTX_OK) return st;
+  for (uint64_t i = 0; i < n; ++i) {
+    const uint32_t k = s->obj_ref[idx[i]] & REF_INDEX_MASK;
+    pack_sphere(&shapes[i].position.x, shapes[i].radius, &s->sph[(size_t)k * SPH_STRIDE]);
+    s->upd_sph.push_back(k);
+    if (materials) update_material(s, idx[i], materials[i]);
+  }
+  if (n) s->bvh_refit = true;
+  return RTX_OK;
+}
+rtx_status rtx_scene_update_planes(rtx_scene* s, const uint64_t* idx, const rtx_plane* shapes, const rtx_material* materials,
+                                   uint64_t n) {
+  if (s == nullptr) return fail(s, RTX_ERR_INVALID_ARGUMENT, "null scene");
+  std::lock_guard<std::mutex> lk(s->mu);
+  rtx_status st = check_update(s, idx, shapes, n, REF_PLANE);
+  if (st != RTX_OK) return st;
+  for (uint64_t i = 0; i < n; ++i) {  // planes are outside the trees: nothing to refit
+    const uint32_t k = s->obj_ref[idx[i]] & REF_INDEX_MASK;
+    pack_plane(&shapes[i].position.x, &shapes[i].normal.x, &s->pl[(size_t)k * PL_STRIDE]);
+    s->upd_pl.push_back(k);
+    if (materials) update_material(s, idx[i], materials[i]);
+  }
+  return RTX_OK;
+}
+rtx_status rtx_scene_update_triangles(rtx_scene* s, const uint64_t* idx, const rtx_triangle* shapes,
+                                      const rtx_material* materials, uint64_t n) {
+  if (s == nullptr) return fail(s, RTX_ERR_INVALID_ARGUMENT, "null scene");
+  std::lock_guard<std::mutex> lk(s->mu);
+  rtx_status st = check_update(s, idx, shapes, n, REF_TRIANGLE);
+  if (st != RTX_OK) return st;
+  for (uint64_t i = 0; i < n; ++i) {
+    const uint32_t k = s->obj_ref[idx[i]] & REF_INDEX_MASK;
+    double* rec = &s->tri[(size_t)k * TRI_STRIDE];
+    uint64_t old_code, new_code;
+    std::memcpy(&old_code, &rec[13], 8);
+    pack_triangle(&shapes[i].vertices[0].x, rec);
+    std::memcpy(&new_code, &rec[13], 8);
+    std::memcpy(&s->tri_raw[(size_t)k * 9], &shapes[i].vertices[0].x, 9 * sizeof(double));
+    s->upd_tri.push_back(k);
+    // the pivots decide which prism tree holds the triangle, the flags whether any tree does
+    if (old_code != new_code) s->bvh_valid = false;
+    if (materials) update_material(s, idx[i], materials[i]);
+  }
+  if (n) s->bvh_refit = true;
+  return RTX_OK;
+}
+rtx_status rtx_scene_rebuild_accel(rtx_scene* s) {
+  if (!s) return fail(s, RTX_ERR_INVALID_ARGUMENT, "null scene");
+  std::lock_guard<std::mutex> lk(s->mu);
+  s->bvh_valid = false;
+  return RTX_OK;
+}
+
+uint32_t rtx_scene_accel_refits(const rtx_scene* s) { return s ? s->bvh_refits : 0; }
+uint32_t rtx_scene_accel_builds(const rtx_scene* s) { return s ? s->bvh_builds : 0; }
+
 rtx_status rtx_scene_clear_objects(rtx_scene* s) {
   if (!s) return fail(s, RTX_ERR_INVALID_ARGUMENT, "null scene");
   std::lock_guard<std::mutex> lk(s->mu);
   s->sph.clear(), s->pl.clear(), s->tri.clear(), s->mat.clear(), s->tri_raw.clear();
-  s->sph_id.clear(), s->pl_id.clear(), s->tri_id.clear();
+  s->sph_id.clear(), s->pl_id.clear(), s->tri_id.clear(), s->obj_ref.clear();
+  s->upd_sph.clear(), s->upd_pl.clear(), s->upd_tri.clear(), s->upd_mat.clear();
   s->n_obj = 0;
   s->dirty = true;
   s->bvh_valid = false;

@@ -22,8 +22,11 @@ struct rtx_scene {
   std::vector<double> sph, pl, tri, mat;
   std::vector<uint32_t> sph_id, pl_id, tri_id;
   std::vector<double> tri_raw;  // 9 doubles per triangle: the LBVH builder needs the vertices for boxes
+  std::vector<uint32_t> obj_ref;  // per object: REF_* | index within its shape array
   uint64_t n_obj = 0;
-  bool dirty = true;
+  bool dirty = true;              // layout changed: rebuild and upload the whole blob
+  // in-place updates since the last upload (indices within the shape arrays / object indices for materials)
+  std::vector<uint32_t> upd_sph, upd_pl, upd_tri, upd_mat;
 
   // device copies
   unsigned char* d_blob = nullptr;
@@ -36,6 +39,17 @@ struct rtx_scene {
   uint32_t bvh_count[4] = {0, 0, 0, 0};
   uint32_t bvh_build_launches = 0;
   bool bvh_valid = false;
+  bool bvh_refit = false;   // primitives moved since the trees were built/refitted: same hierarchy, new boxes
+  uint32_t bvh_refits = 0, bvh_builds = 0;  // refits / full builds performed (statistics)
+  // what a refit needs of each tree: its primitive list, validity, sorted order and hierarchy
+  struct TreeTopo {
+    uint32_t n = 0, m = 0;
+    int open_axis = 3;
+    uint32_t *d_prims = nullptr, *d_vals = nullptr, *d_left = nullptr, *d_right = nullptr, *d_parent = nullptr;
+    uint8_t* d_valid = nullptr;
+  } topo[4];
+  double* d_tri_raw = nullptr;  // device copy of tri_raw (boxes are computed from the vertices)
+  size_t d_tri_raw_cap = 0;
 
   // separable sin/cos tables of get_ray_dir, cached per (width, height, fov)
   double* d_tables = nullptr;  // [sin_x W][cos_x W][sin_y H][cos_y H]

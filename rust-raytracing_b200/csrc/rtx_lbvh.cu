@@ -228,12 +228,20 @@ __global__ void k_hierarchy(const uint64_t* __restrict__ keys, int m, uint32_t* 
 }
 
 // ---- 5. leaves + bottom-up refit (second arrival at a node merges its children) --------------------------------
+// pad = 2^-20 x scene scale (largest |coordinate| of the finite box corners; see rtx_lbvh.cuh)
+__device__ __forceinline__ double box_pad(const double* __restrict__ bounds) {
+  double scale = 1e-300;
+  for (int k = 0; k < 6; ++k) scale = fmax(scale, fabs(bounds[k]));
+  return scale * 9.5367431640625e-07;
+}
 __global__ void k_refit(const uint32_t* __restrict__ sorted_vals, const uint32_t* __restrict__ prims,
-                        const double* __restrict__ lo, const double* __restrict__ hi, int m, double pad,
-                        const uint32_t* __restrict__ left, const uint32_t* __restrict__ right,
-                        const uint32_t* __restrict__ parent, uint32_t* __restrict__ flags, BvhNode* __restrict__ nodes) {
+                        const double* __restrict__ lo, const double* __restrict__ hi, int m,
+                        const double* __restrict__ bounds, const uint32_t* __restrict__ left,
+                        const uint32_t* __restrict__ right, const uint32_t* __restrict__ parent,
+                        uint32_t* __restrict__ flags, BvhNode* __restrict__ nodes) {
   const int j = blockIdx.x * blockDim.x + threadIdx.x;
   if (j >= m) return;
+  const double pad = box_pad(bounds);
   const uint32_t src = sorted_vals[j];
   const uint32_t self = (uint32_t)(m - 1 + j);
   BvhNode nd;
@@ -315,6 +323,12 @@ __global__ void k_count_valid(const uint64_t* __restrict__ sorted_keys, uint32_t
   if (sorted_keys[i] == ~0ULL && (i == 0 || sorted_keys[i - 1] != ~0ULL)) *out = i;
 }
 
+// refit precondition: the set of primitives inside the tree is unchanged
+__global__ void k_valid_diff(const uint8_t* __restrict__ a, const uint8_t* __restrict__ b, uint32_t n, uint32_t* __restrict__ out) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n && a[i] != b[i]) atomicAdd(out, 1u);
+}
+
 // ---- host orchestration ---------------------------------------------------------------------------------------
 template <typename T>
 struct Tmp {
@@ -323,6 +337,11 @@ struct Tmp {
     if (p) cudaFree(p);
   }
   cudaError_t alloc(size_t n) { return cudaMalloc((void**)&p, (n ? n : 1) * sizeof(T)); }
+  T* release() {
+    T* q = p;
+    p = nullptr;
+    return q;
+  }
 };
 
 #define LBVH_TRY(expr)                                          \
@@ -332,12 +351,19 @@ struct Tmp {
   } while (0)
 
 // Builds one tree over `prims` (host list of REF_*|index).  Synchronous on `stream`.
+static void free_topo(rtx_scene::TreeTopo& t) {
+  cudaFree(t.d_prims), cudaFree(t.d_vals), cudaFree(t.d_left), cudaFree(t.d_right), cudaFree(t.d_parent), cudaFree(t.d_valid);
+  t = rtx_scene::TreeTopo{};
+}
+
 static rtx_status build_tree(rtx_scene* s, const std::vector<uint32_t>& prims, int open_axis, const double* d_tri_raw,
                              cudaStream_t stream, WideNode** out_nodes, uint32_t* out_root, uint32_t* out_count,
-                             uint32_t* launches) {
+                             uint32_t* launches, rtx_scene::TreeTopo* topo) {
   *out_nodes = nullptr;
   *out_root = BVH_END;
   *out_count = 0;
+  free_topo(*topo);
+  topo->open_axis = open_axis;
   const uint32_t n = (uint32_t)prims.size();
   if (n == 0) return RTX_OK;
   const unsigned B = 256, G = (n + B - 1) / B;
@@ -381,14 +407,9 @@ static rtx_status build_tree(rtx_scene* s, const std::vector<uint32_t>& prims, i
   k_count_valid<<<G, B, 0, stream>>>(d_keys[cur].p, n, d_m.p);
   *launches += 1;
   uint32_t m = 0;
-  double hb[6];
   LBVH_TRY(cudaMemcpyAsync(&m, d_m.p, 4, cudaMemcpyDeviceToHost, stream));
-  LBVH_TRY(cudaMemcpyAsync(hb, d_bounds.p, sizeof(hb), cudaMemcpyDeviceToHost, stream));
   LBVH_TRY(cudaStreamSynchronize(stream));
   if (m == 0) return RTX_OK;
-  double scale = 1e-300;
-  for (int k = 0; k < 6; ++k) scale = std::fmax(scale, std::fabs(hb[k]));
-  const double pad = scale * 9.5367431640625e-07;  // 2^-20 x scene scale (see rtx_lbvh.cuh)
   const uint32_t total = 2 * m - 1;
   BvhNode* nodes = nullptr;  // f64 build nodes (freed below); the traversal gets the f32 two-box nodes
   WideNode* wide = nullptr;
@@ -413,8 +434,8 @@ static rtx_status build_tree(rtx_scene* s, const std::vector<uint32_t>& prims, i
     }
     const unsigned Gm = (m + B - 1) / B;
     if (m > 1) k_hierarchy<<<Gm, B, 0, stream>>>(d_keys[cur].p, (int)m, d_left.p, d_right.p, d_parent.p);
-    k_refit<<<Gm, B, 0, stream>>>(d_vals[cur].p, d_prims.p, d_lo.p, d_hi.p, (int)m, pad, d_left.p, d_right.p, d_parent.p,
-                                  d_flags.p, nodes);
+    k_refit<<<Gm, B, 0, stream>>>(d_vals[cur].p, d_prims.p, d_lo.p, d_hi.p, (int)m, d_bounds.p, d_left.p, d_right.p,
+                                  d_parent.p, d_flags.p, nodes);
     k_emit_wide<<<Gm, B, 0, stream>>>((int)m, nodes, d_left.p, d_right.p, wide);
     *launches += 3;
     if ((e = cudaGetLastError()) != cudaSuccess || (e = cudaStreamSynchronize(stream)) != cudaSuccess) {
@@ -430,6 +451,57 @@ static rtx_status build_tree(rtx_scene* s, const std::vector<uint32_t>& prims, i
   *out_nodes = wide;
   *out_root = 0u;  // the root is wide node 0
   *out_count = n_wide;
+  // keep what a refit needs: primitive list, validity, sorted order, hierarchy
+  topo->n = n, topo->m = m;
+  topo->d_prims = d_prims.release();
+  topo->d_vals = d_vals[cur].release();
+  topo->d_left = d_left.release();
+  topo->d_right = d_right.release();
+  topo->d_parent = d_parent.release();
+  topo->d_valid = d_valid.release();
+  return RTX_OK;
+}
+
+// Same hierarchy, new boxes: recompute the primitive boxes from the (updated) scene, check that the same
+// primitives are inside the tree, then redo the bottom-up pass and the traversal nodes in place.
+// *needs_rebuild is set when membership changed.  Synchronous on `stream`.
+static rtx_status refit_tree(rtx_scene* s, const rtx_scene::TreeTopo& t, WideNode* wide, cudaStream_t stream,
+                             bool* needs_rebuild, uint32_t* launches) {
+  if (t.n == 0 || t.m == 0) return RTX_OK;
+  const unsigned B = 256, G = (t.n + B - 1) / B, Gm = (t.m + B - 1) / B;
+  Tmp<double> d_lo, d_hi, d_bounds;
+  Tmp<uint8_t> d_valid;
+  Tmp<uint32_t> d_flags, d_diff;
+  Tmp<BvhNode> d_nodes;
+  LBVH_TRY(d_lo.alloc((size_t)t.n * 3));
+  LBVH_TRY(d_hi.alloc((size_t)t.n * 3));
+  LBVH_TRY(d_valid.alloc(t.n));
+  LBVH_TRY(d_bounds.alloc(6));
+  LBVH_TRY(d_flags.alloc(t.m));
+  LBVH_TRY(d_diff.alloc(1));
+  LBVH_TRY(d_nodes.alloc((size_t)2 * t.m - 1));
+  const double inf = std::numeric_limits<double>::infinity();
+  const double b0[6] = {inf, inf, inf, -inf, -inf, -inf};
+  LBVH_TRY(cudaMemcpyAsync(d_bounds.p, b0, sizeof(b0), cudaMemcpyHostToDevice, stream));
+  LBVH_TRY(cudaMemsetAsync(d_diff.p, 0, 4, stream));
+  LBVH_TRY(cudaMemsetAsync(d_flags.p, 0, (size_t)t.m * 4, stream));
+  const double* d_sph = reinterpret_cast<const double*>(s->d_blob + s->layout.off_sph);
+  k_prim_boxes<<<G, B, 0, stream>>>(d_sph, s->d_tri_raw, t.d_prims, t.n, t.open_axis, d_lo.p, d_hi.p, d_valid.p, d_bounds.p);
+  k_valid_diff<<<G, B, 0, stream>>>(d_valid.p, t.d_valid, t.n, d_diff.p);
+  uint32_t diff = 0;
+  LBVH_TRY(cudaMemcpyAsync(&diff, d_diff.p, 4, cudaMemcpyDeviceToHost, stream));
+  LBVH_TRY(cudaStreamSynchronize(stream));
+  *launches += 2;
+  if (diff != 0) {
+    *needs_rebuild = true;
+    return RTX_OK;
+  }
+  k_refit<<<Gm, B, 0, stream>>>(t.d_vals, t.d_prims, d_lo.p, d_hi.p, (int)t.m, d_bounds.p, t.d_left, t.d_right, t.d_parent,
+                                d_flags.p, d_nodes.p);
+  k_emit_wide<<<Gm, B, 0, stream>>>((int)t.m, d_nodes.p, t.d_left, t.d_right, wide);
+  *launches += 2;
+  LBVH_TRY(cudaGetLastError());
+  LBVH_TRY(cudaStreamSynchronize(stream));
   return RTX_OK;
 }
 
@@ -439,13 +511,30 @@ void free_lbvh(rtx_scene* s) {
     s->d_bvh[k] = nullptr;
     s->bvh_root[k] = BVH_END;
     s->bvh_count[k] = 0;
+    free_topo(s->topo[k]);
   }
   s->bvh_valid = false;
+  s->bvh_refit = false;
 }
 
 // Builds the 3-D tree (spheres + triangles) and one prism tree per dropped axis (triangles).  The scene blob
 // must be uploaded.  Rebuilt whenever the object list changed.
 rtx_status ensure_lbvh(rtx_scene* s, cudaStream_t stream) {
+  if (s->bvh_valid && s->bvh_refit) {  // rtx_scene_update_*: primitives moved, hierarchy kept
+    bool rebuild = false;
+    uint32_t launches = 0;
+    for (int k = 0; k < 4 && !rebuild; ++k) {
+      if (s->bvh_root[k] == BVH_END) continue;
+      rtx_status st = refit_tree(s, s->topo[k], s->d_bvh[k], stream, &rebuild, &launches);
+      if (st != RTX_OK) return st;
+    }
+    s->bvh_refit = false;
+    if (!rebuild) {
+      ++s->bvh_refits;
+      return RTX_OK;
+    }
+    s->bvh_valid = false;
+  }
   if (s->bvh_valid) return RTX_OK;
   free_lbvh(s);
   const uint32_t n_sph = (uint32_t)s->sph_id.size(), n_tri = (uint32_t)s->tri_id.size();
@@ -460,22 +549,28 @@ rtx_status ensure_lbvh(rtx_scene* s, cudaStream_t stream) {
     const int i1 = (int)((code >> TRI_I1_SHIFT) & 3), i2 = (int)((code >> TRI_I2_SHIFT) & 3);
     prism[3 - i1 - i2].push_back(REF_TRIANGLE | i);  // the coordinate contains() never looks at
   }
-  Tmp<double> d_tri_raw;
-  if (n_tri) {
-    LBVH_TRY(d_tri_raw.alloc(s->tri_raw.size()));
-    LBVH_TRY(cudaMemcpyAsync(d_tri_raw.p, s->tri_raw.data(), s->tri_raw.size() * 8, cudaMemcpyHostToDevice, stream));
+  if (n_tri) {  // persistent: refits recompute boxes from it
+    if (s->d_tri_raw_cap < s->tri_raw.size() * 8 || !s->d_tri_raw) {
+      cudaFree(s->d_tri_raw);
+      s->d_tri_raw = nullptr, s->d_tri_raw_cap = 0;
+      LBVH_TRY(cudaMalloc((void**)&s->d_tri_raw, s->tri_raw.size() * 8));
+      s->d_tri_raw_cap = s->tri_raw.size() * 8;
+    }
+    LBVH_TRY(cudaMemcpyAsync(s->d_tri_raw, s->tri_raw.data(), s->tri_raw.size() * 8, cudaMemcpyHostToDevice, stream));
   }
   uint32_t launches = 0;
-  rtx_status st = build_tree(s, all, 3, d_tri_raw.p, stream, &s->d_bvh[0], &s->bvh_root[0], &s->bvh_count[0], &launches);
+  rtx_status st = build_tree(s, all, 3, s->d_tri_raw, stream, &s->d_bvh[0], &s->bvh_root[0], &s->bvh_count[0], &launches,
+                             &s->topo[0]);
   for (int a = 0; a < 3 && st == RTX_OK; ++a)
-    st = build_tree(s, prism[a], a, d_tri_raw.p, stream, &s->d_bvh[1 + a], &s->bvh_root[1 + a], &s->bvh_count[1 + a],
-                    &launches);
+    st = build_tree(s, prism[a], a, s->d_tri_raw, stream, &s->d_bvh[1 + a], &s->bvh_root[1 + a], &s->bvh_count[1 + a],
+                    &launches, &s->topo[1 + a]);
   if (st != RTX_OK) {
     free_lbvh(s);
     return st;
   }
   s->bvh_build_launches = launches;
   s->bvh_valid = true;
+  ++s->bvh_builds;
   return RTX_OK;
 }
 

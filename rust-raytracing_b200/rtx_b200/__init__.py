@@ -289,6 +289,58 @@ class Scene:
         else:
             self._batches.append((kind, shapes, materials))
 
+    def update_objects(self, indices, shapes, materials=None):
+        """In-place replacement of existing objects (rtx_scene_update_*): `indices` = global object indices, all
+        of one shape kind; `shapes` = rows in this module's layout (sphere: c.xyz r; plane: pos.xyz n.xyz;
+        triangle: 9 doubles); `materials` = rows (base.xyz, emission.xyz, roughness) or None to keep them.
+        Only the touched records are re-uploaded and the LBVH is refitted instead of rebuilt."""
+        indices = np.ascontiguousarray(indices, dtype=np.uint64).reshape(-1)
+        shapes = np.ascontiguousarray(shapes, dtype=np.float64).reshape(indices.shape[0], -1)
+        if materials is not None:
+            materials = np.ascontiguousarray(materials, dtype=np.float64).reshape(indices.shape[0], 7)
+        # locate every object in the host-side batches
+        starts = np.cumsum([0] + [b[1].shape[0] for b in self._batches])
+        kinds = set()
+        where = []
+        for i in indices.tolist():
+            if not 0 <= i < starts[-1]:
+                raise RtxError(_abi.RTX_ERR_INVALID_ARGUMENT, "object index out of range")
+            b = int(np.searchsorted(starts, i, side="right") - 1)
+            kinds.add(self._batches[b][0])
+            where.append((b, i - int(starts[b])))
+        if len(kinds) > 1:
+            raise RtxError(_abi.RTX_ERR_INVALID_ARGUMENT, "objects of different shape kinds in one update")
+        if not where:
+            return
+        kind = kinds.pop()
+        ncol = {SHAPE_SPHERE: 4, SHAPE_PLANE: 6, SHAPE_TRIANGLE: 9}[kind]
+        if shapes.shape[1] != ncol:
+            raise RtxError(_abi.RTX_ERR_INVALID_ARGUMENT, "shape rows have the wrong width for this kind")
+        for (b, r), row, k in zip(where, shapes, range(len(where))):
+            self._batches[b][1][r] = row
+            if materials is not None:
+                self._batches[b][2][r] = materials[k]
+        if self._handle is not None and all(b < self._synced_batches for b, _ in where):
+            fn = {SHAPE_SPHERE: "rtx_scene_update_spheres", SHAPE_PLANE: "rtx_scene_update_planes",
+                  SHAPE_TRIANGLE: "rtx_scene_update_triangles"}[kind]
+            _abi.check(getattr(_abi.load(), fn)(self._handle, indices.ctypes.data, shapes.ctypes.data,
+                                                materials.ctypes.data if materials is not None else None,
+                                                indices.shape[0]), self._handle)
+        elif self._handle is not None:  # some of them were never uploaded: start over
+            self.close()
+
+    def rebuild_accel(self):
+        if self._handle is not None:
+            _abi.check(_abi.load().rtx_scene_rebuild_accel(self._handle), self._handle)
+
+    @property
+    def accel_refits(self):
+        return int(_abi.load().rtx_scene_accel_refits(self._handle)) if self._handle is not None else 0
+
+    @property
+    def accel_builds(self):
+        return int(_abi.load().rtx_scene_accel_builds(self._handle)) if self._handle is not None else 0
+
     def add_wire_objects(self, records, buffers):
         """≙ gpu::Scene::add_object's serialized state (gpu/gpu_state.rs:53-77): 48-byte object records plus one
         (object_type tag, bytes, count) shape buffer per shape_id, in the reference's f32 wire format (wire.py)."""

@@ -51,6 +51,12 @@ pub const RTX_FLAG_SAMPLE_QUEUE: u32 = 64;
 pub const RTX_PEER_HANDLE_BYTES: usize = 64;
 
 extern "C" {
+    pub fn rtx_scene_update_spheres(scene: *mut rtx_scene, object_indices: *const u64, shapes: *const rtx_sphere, materials: *const rtx_material, n: u64) -> rtx_status;
+    pub fn rtx_scene_update_planes(scene: *mut rtx_scene, object_indices: *const u64, shapes: *const rtx_plane, materials: *const rtx_material, n: u64) -> rtx_status;
+    pub fn rtx_scene_update_triangles(scene: *mut rtx_scene, object_indices: *const u64, shapes: *const rtx_triangle, materials: *const rtx_material, n: u64) -> rtx_status;
+    pub fn rtx_scene_rebuild_accel(scene: *mut rtx_scene) -> rtx_status;
+    pub fn rtx_scene_accel_refits(scene: *const rtx_scene) -> u32;
+    pub fn rtx_scene_accel_builds(scene: *const rtx_scene) -> u32;
     pub fn rtx_peer_alloc(device: i32, bytes: u64, out_d_ptr: *mut *mut c_void) -> rtx_status;
     pub fn rtx_peer_free(device: i32, d_ptr: *mut c_void) -> rtx_status;
     pub fn rtx_peer_export(device: i32, d_ptr: *mut c_void, out_handle: *mut u8) -> rtx_status;
