@@ -265,10 +265,7 @@ static rtx_status render_common(rtx_scene* s, uint32_t width, uint32_t height, u
   p.use_bvh = use_bvh ? 1u : 0u;
   p.lane_kernel = (flags & RTX_FLAG_LANE_KERNEL) ? 1u : 0u;
   p.queue_mode = (flags & RTX_FLAG_PIXEL_QUEUE) ? 1u : ((flags & RTX_FLAG_SAMPLE_QUEUE) ? 2u : 0u);
-  for (int k = 0; k < 4; ++k) {
-    p.bvh.nodes[k] = use_bvh ? s->d_bvh[k] : nullptr;
-    p.bvh.root[k] = use_bvh ? s->bvh_root[k] : BVH_END;
-  }
+  fill_bvh_view(s, use_bvh, &p.bvh);
   p.shard_index = sh.index, p.shard_count = sh.count;
   p.tiles_x = (width + TILE - 1) / TILE, p.tiles_y = (height + TILE - 1) / TILE;
   p.my_tiles = (uint32_t)shard_tiles(width, height, sh.index, sh.count);

@@ -109,12 +109,11 @@ rtx_status rtx_debug_closest_object(rtx_scene* s, uint32_t flags, const double* 
   if (st != RTX_OK) return st;
   const bool use_bvh = choose_accel(s, flags) == RTX_ACCEL_LBVH;
   BvhView bv{};
-  for (int k = 0; k < 4; ++k) bv.root[k] = BVH_END;
   if (use_bvh) {
     st = ensure_lbvh(s, s->stream);
     if (st != RTX_OK) return st;
-    for (int k = 0; k < 4; ++k) bv.nodes[k] = s->d_bvh[k], bv.root[k] = s->bvh_root[k];
   }
+  fill_bvh_view(s, use_bvh, &bv);
   if (n == 0) return RTX_OK;
   DevBuf<double> d_rays, d_t;
   DevBuf<uint32_t> d_id;

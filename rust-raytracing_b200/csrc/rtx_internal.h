@@ -48,6 +48,8 @@ struct rtx_scene {
     uint32_t *d_prims = nullptr, *d_vals = nullptr, *d_left = nullptr, *d_right = nullptr, *d_parent = nullptr;
     uint8_t* d_valid = nullptr;
   } topo[4];
+  float prism_s[4] = {1, 1, 1, 1}, prism_z[4] = {0, 0, 0, 0};  // per prism tree: normal bounds (rtx_lbvh.cuh)
+  int prism_sign[4] = {0, 0, 0, 0};
   double* d_tri_raw = nullptr;  // device copy of tri_raw (boxes are computed from the vertices)
   size_t d_tri_raw_cap = 0;
 
@@ -91,6 +93,7 @@ cudaError_t launch_render_pool(const RenderParams& p, int sm_count, cudaStream_t
 // Builds the LBVH trees if the object list changed since the last build.  Synchronous.
 rtx_status ensure_lbvh(rtx_scene* s, cudaStream_t stream);
 void free_lbvh(rtx_scene* s);
+void fill_bvh_view(const rtx_scene* s, bool use_bvh, BvhView* bv);
 // Which structure a render with these flags will use (RTX_ACCEL_BRUTE or RTX_ACCEL_LBVH).
 uint32_t choose_accel(const rtx_scene* s, uint32_t flags);
 }  // namespace rtx

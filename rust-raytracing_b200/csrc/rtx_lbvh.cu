@@ -38,7 +38,8 @@ __device__ __forceinline__ void atomic_max_f64(double* addr, double v) {
 }
 
 // ---- 1. per-primitive boxes + scene bounds ------------------------------------------------------------------
-// prims[i] = REF_* | index.  open_axis in {0,1,2}: that axis is opened to (-inf,+inf) (prism trees); 3: none.
+// prims[i] = REF_* | index.  open_axis in {0,1,2}: prism tree over that dropped axis (it contributes nothing to
+// the Morton code); 3: the 3-D tree.
 // Primitives that can never be hit (non-finite data) get valid = 0: they are left out of the tree.
 // bounds[0..2] = min, [3..5] = max over the finite box corners (used for Morton quantisation and padding).
 __global__ void k_prim_boxes(const double* __restrict__ sph /* cx cy cz r2 */, const double* __restrict__ tri_raw /* 9/tri */,
@@ -70,7 +71,8 @@ __global__ void k_prim_boxes(const double* __restrict__ sph /* cx cy cz r2 */, c
       atomic_min_f64(&bounds[k], l[k]);
       atomic_max_f64(&bounds[3 + k], h[k]);
     }
-    if (open_axis < 3) l[open_axis] = -CUDART_INF, h[open_axis] = CUDART_INF;
+    // prism trees keep the true extent along the dropped axis too: the traversal ignores it for the entry
+    // test (the reported point of a phantom hit may be anywhere along it) but uses it for its |t| bounds
   }
   for (int k = 0; k < 3; ++k) lo[(size_t)i * 3 + k] = l[k], hi[(size_t)i * 3 + k] = h[k];
 }
@@ -517,10 +519,54 @@ void free_lbvh(rtx_scene* s) {
   s->bvh_refit = false;
 }
 
+// S, Z and the sign flag of every prism tree (rtx_lbvh.cuh), from the packed triangle records: n = rec[3..5] is the
+// unit normal the distance function uses, the pivots say which axis contains() drops.
+static void compute_prism_constants(rtx_scene* s) {
+  double smax[3] = {0, 0, 0}, zmin[3] = {1, 1, 1};
+  bool pos[3] = {false, false, false}, neg[3] = {false, false, false}, any[3] = {false, false, false};
+  const size_t n_tri = s->tri_id.size();
+  for (size_t i = 0; i < n_tri; ++i) {
+    const double* rec = &s->tri[i * TRI_STRIDE];
+    uint64_t code;
+    std::memcpy(&code, &rec[13], 8);
+    if (code & (TRI_DEGENERATE | TRI_PANIC)) continue;
+    const int i1 = (int)((code >> TRI_I1_SHIFT) & 3), i2 = (int)((code >> TRI_I2_SHIFT) & 3), a = 3 - i1 - i2;
+    const double na = rec[3 + a], nb = rec[3 + (a + 1) % 3], nc = rec[3 + (a + 2) % 3];
+    any[a] = true;
+    if (!(na - na == 0.0) || !(nb - nb == 0.0) || !(nc - nc == 0.0)) {  // non-finite normal: no bound holds
+      smax[a] = std::numeric_limits<double>::infinity();
+      zmin[a] = 0.0;
+      pos[a] = neg[a] = true;
+      continue;
+    }
+    smax[a] = std::fmax(smax[a], std::sqrt(nb * nb + nc * nc));
+    zmin[a] = std::fmin(zmin[a], std::fabs(na));
+    (na > 0.0 ? pos[a] : neg[a]) = true;  // n_a == 0 counts as "mixed" through zmin = 0 anyway
+  }
+  for (int a = 0; a < 3; ++a) {
+    const float sf = (float)(smax[a] * 1.000001), zf = (float)(zmin[a] * 0.999999);
+    s->prism_s[1 + a] = any[a] ? std::nextafterf(sf, std::numeric_limits<float>::infinity()) : 1.0f;
+    s->prism_z[1 + a] = any[a] ? std::fmax(0.0f, std::nextafterf(zf, 0.0f)) : 0.0f;
+    s->prism_sign[1 + a] = (pos[a] && !neg[a]) ? 1 : ((neg[a] && !pos[a]) ? -1 : 0);
+  }
+  s->prism_s[0] = 1.0f, s->prism_z[0] = 0.0f, s->prism_sign[0] = 0;
+}
+
+void fill_bvh_view(const rtx_scene* s, bool use_bvh, BvhView* bv) {
+  for (int k = 0; k < 4; ++k) {
+    bv->nodes[k] = use_bvh ? s->d_bvh[k] : nullptr;
+    bv->root[k] = use_bvh ? s->bvh_root[k] : BVH_END;
+    bv->prism_s[k] = s->prism_s[k];
+    bv->prism_z[k] = s->prism_z[k];
+    bv->prism_sign[k] = s->prism_sign[k];
+  }
+}
+
 // Builds the 3-D tree (spheres + triangles) and one prism tree per dropped axis (triangles).  The scene blob
 // must be uploaded.  Rebuilt whenever the object list changed.
 rtx_status ensure_lbvh(rtx_scene* s, cudaStream_t stream) {
   if (s->bvh_valid && s->bvh_refit) {  // rtx_scene_update_*: primitives moved, hierarchy kept
+    compute_prism_constants(s);
     bool rebuild = false;
     uint32_t launches = 0;
     for (int k = 0; k < 4 && !rebuild; ++k) {
@@ -549,6 +595,7 @@ rtx_status ensure_lbvh(rtx_scene* s, cudaStream_t stream) {
     const int i1 = (int)((code >> TRI_I1_SHIFT) & 3), i2 = (int)((code >> TRI_I2_SHIFT) & 3);
     prism[3 - i1 - i2].push_back(REF_TRIANGLE | i);  // the coordinate contains() never looks at
   }
+  compute_prism_constants(s);
   if (n_tri) {  // persistent: refits recompute boxes from it
     if (s->d_tri_raw_cap < s->tri_raw.size() * 8 || !s->d_tri_raw) {
       cudaFree(s->d_tri_raw);

@@ -14,8 +14,18 @@
 // Triangles need a second kind of tree.  A "phantom" hit (plane BEHIND the ray, distance = |t|,
 // triangle.rs:118) reports the mirrored point pos + dir*|t|, which is off the plane and only has to lie in
 // the infinite prism over the triangle's projection along the coordinate contains() drops
-// (triangle.rs:96-100).  It is bounded by the triangle's box with that axis opened to (-inf, +inf).  One
-// such "prism tree" per dropped axis is traversed after the 3-D tree, pruned by the best distance so far.
+// (triangle.rs:96-100).  One "prism tree" per dropped axis a is traversed after the 3-D tree.  Its nodes keep
+// the triangles' true 3-D boxes, but a node is entered on the evidence of the two KEPT axes only (the reported
+// point may be anywhere along a), pruned by the best distance so far and by two bounds that hold for every
+// triangle T below the node (unit normal n, |n_perp| <= S, |n_a| >= Z; v0 inside the node's box):
+//  (A) "not a phantom": if the node lies wholly ahead of the origin along a (distance >= g > 0 in the direction
+//      the ray travels along a), g*Z > S*dperp_max and |d_a|*Z > |d_perp|*S, then for every T both n.(v0 - pos)
+//      and d.n take the sign of n_a (their a-terms dominate): the plane is in FRONT, the hit is an ordinary
+//      one and the 3-D tree finds it;
+//  (B) |t| = |n.(v0 - pos)| / |d.n| <= (S*dperp_max + da_max) / (|d_a|*Z - |d_perp|*S) =: U when the denominator
+//      is positive: the reported point lies at parameter <= U, so a node whose kept-axes entry parameter exceeds
+//      U cannot contain it.
+// Without them a ray that leaves a height field upwards walks the footprint of every triangle under its path.
 #pragma once
 #include "rtx_trace.cuh"
 
@@ -47,6 +57,11 @@ struct __align__(16) WideNode {  // 64 B = four 128-bit loads
 struct BvhView {
   const WideNode* nodes[4];  // [0] 3-D tree over spheres + triangles; [1..3] prism trees (dropped axis x,y,z)
   uint32_t root[4];          // BVH_END when the tree is empty, else 0
+  // Per prism tree (index 1 + a, a = dropped axis), over its triangles' unit normals n:
+  //   prism_s >= max |n without its a-component|, prism_z <= min |n_a|  (rounded outward),
+  //   prism_sign = +1 / -1 when every n_a has that sign, 0 when mixed.
+  float prism_s[4], prism_z[4];
+  int prism_sign[4];
 };
 
 #if defined(__CUDACC__)
@@ -95,6 +110,56 @@ RTX_D bool box_test(const float* lo, const float* hi, const RayF32& r, float bes
   return !(tfar < fmaxf(tnear, 0.0f)) && !(tnear > best_up);
 }
 
+// Per-ray constants of one prism tree (dropped axis a).
+struct PrismRay {
+  int a, b, c;      // dropped axis, kept axes
+  float den;        // lower bound of |d.n| over the tree's triangles: |d_a|*Z - |d_perp|*S (<= 0: no bound)
+  float s, z;       // the tree's S and Z
+  bool sign_known;  // all n_a of one sign
+};
+RTX_D PrismRay make_prism_ray(const BvhView& bv, int tree, V3 dn) {
+  PrismRay pr;
+  pr.a = tree - 1;
+  pr.b = (pr.a + 1) % 3;
+  pr.c = (pr.a + 2) % 3;
+  const double d[3] = {dn.x, dn.y, dn.z};
+  pr.s = bv.prism_s[tree];
+  pr.z = bv.prism_z[tree];
+  pr.sign_known = bv.prism_sign[tree] != 0;
+  const float da = __double2float_rd(fabs(d[pr.a]) * 0.999999);
+  const float dp = __double2float_ru(sqrt(d[pr.b] * d[pr.b] + d[pr.c] * d[pr.c]) * 1.000001);
+  pr.den = __fsub_rd(__fmul_rd(da, pr.z), __fmul_ru(dp, pr.s));
+  return pr;
+}
+// Entry test of a prism-tree node: slabs on the kept axes, then bounds (A) and (B) above.  All roundings are
+// directed so that a node is only skipped when the exact-arithmetic statement holds with margin; the f64
+// quantities they bound (|t| as computed by triangle_distance, the reported point) differ from the exact ones
+// by ~1e-16 relative, far inside the 1e-6 margins and the 2^-20 box padding.
+RTX_D bool box_test_prism(const float* lo, const float* hi, const RayF32& r, const PrismRay& pr, float best_up, float& tnear) {
+  float tnb, tfb, tnc, tfc;
+  slab(lo[pr.b], hi[pr.b], r.neg[pr.b], r.o_dn[pr.b], r.o_up[pr.b], r.inv_dn[pr.b], r.inv_up[pr.b], tnb, tfb);
+  slab(lo[pr.c], hi[pr.c], r.neg[pr.c], r.o_dn[pr.c], r.o_up[pr.c], r.inv_dn[pr.c], r.inv_up[pr.c], tnc, tfc);
+  tnear = fmaxf(tnb, tnc);
+  const float tfar = fminf(tfb, tfc);
+  if ((tfar < fmaxf(tnear, 0.0f)) || (tnear > best_up)) return false;
+  if (!(pr.den > 0.0f)) return true;
+  // mirrored coordinates (the ray travels towards + on every axis): box [l, h], origin in [o_dn, o_up]
+  const float lb = r.neg[pr.b] ? -hi[pr.b] : lo[pr.b], hb = r.neg[pr.b] ? -lo[pr.b] : hi[pr.b];
+  const float lc = r.neg[pr.c] ? -hi[pr.c] : lo[pr.c], hc = r.neg[pr.c] ? -lo[pr.c] : hi[pr.c];
+  const float la = r.neg[pr.a] ? -hi[pr.a] : lo[pr.a], ha = r.neg[pr.a] ? -lo[pr.a] : hi[pr.a];
+  const float db = fmaxf(__fsub_ru(hb, r.o_dn[pr.b]), __fsub_ru(r.o_up[pr.b], lb));  // >= max |v_b - p_b|
+  const float dc = fmaxf(__fsub_ru(hc, r.o_dn[pr.c]), __fsub_ru(r.o_up[pr.c], lc));
+  const float dperp = __fmul_ru(__fsqrt_ru(__fadd_ru(__fmul_ru(db, db), __fmul_ru(dc, dc))), 1.000001f);
+  const float sd = __fmul_ru(pr.s, dperp);
+  // (A): wholly ahead along a, and far enough that the a-term decides the sign of n.(v0 - pos)
+  const float gap = __fsub_rd(la, r.o_up[pr.a]);
+  if (gap > 0.0f && __fmul_rd(gap, pr.z) > sd) return false;
+  // (B): upper bound of |t|
+  const float da = fmaxf(__fsub_ru(ha, r.o_dn[pr.a]), __fsub_ru(r.o_up[pr.a], la));
+  const float u = __fmul_ru(__fdiv_ru(__fadd_ru(sd, da), pr.den), 1.00001f);
+  return !(tnear > u);
+}
+
 template <bool PRISM>
 RTX_D void bvh_leaf_test(const SceneView& sc, uint32_t child, V3 pos, V3 dir, const RayInv& ri, Hit& h,
                          uint32_t* panics) {
@@ -122,7 +187,7 @@ RTX_D void bvh_leaf_test(const SceneView& sc, uint32_t child, V3 pos, V3 dir, co
 // Near-first walk with a short per-thread stack of (child ref, entry bound).
 template <bool PRISM>
 RTX_D void bvh_walk(const WideNode* __restrict__ nodes, const SceneView& sc, V3 pos, V3 dir, const RayInv& ri,
-                    const RayF32& rf, Hit& h, uint32_t* panics, TraversalCounters& tc) {
+                    const RayF32& rf, const PrismRay& pr, Hit& h, uint32_t* panics, TraversalCounters& tc) {
   uint32_t stack_ref[128];
   float stack_t[128];
   int sp = 0;
@@ -142,8 +207,8 @@ RTX_D void bvh_walk(const WideNode* __restrict__ nodes, const SceneView& sc, V3 
       const float lo1[3] = {q1.z, q1.w, q2.x}, hi1[3] = {q2.y, q2.z, q2.w};
       const float best_up = __double2float_ru(h.t);
       float t0, t1;
-      const bool v0 = box_test(lo0, hi0, rf, best_up, t0);
-      const bool v1 = box_test(lo1, hi1, rf, best_up, t1);
+      const bool v0 = PRISM ? box_test_prism(lo0, hi0, rf, pr, best_up, t0) : box_test(lo0, hi0, rf, best_up, t0);
+      const bool v1 = PRISM ? box_test_prism(lo1, hi1, rf, pr, best_up, t1) : box_test(lo1, hi1, rf, best_up, t1);
       if (v0 && v1) {
         const bool first0 = t0 <= t1;
         // depth <= 64 key bits + 32 index bits (Karras: every level lengthens the common prefix), so 128 holds
@@ -186,10 +251,15 @@ RTX_D Hit closest_lbvh(const SceneView& sc, const BvhView& bv, V3 pos, V3 dir, u
   tc.prims += sc.n_pl;
   // slab parameters are in units of dn, like every distance the shapes return
   const RayF32 rf = make_ray_f32(pos, ri.dn);
-  if (bv.root[0] != BVH_END) bvh_walk<false>(bv.nodes[0], sc, pos, dir, ri, rf, h, panics, tc);
+  PrismRay pr;
+  pr.a = 0, pr.b = 1, pr.c = 2, pr.den = 0.0f, pr.s = 1.0f, pr.z = 0.0f, pr.sign_known = false;
+  if (bv.root[0] != BVH_END) bvh_walk<false>(bv.nodes[0], sc, pos, dir, ri, rf, pr, h, panics, tc);
 #pragma unroll 1
   for (int k = 1; k < 4; ++k)
-    if (bv.root[k] != BVH_END) bvh_walk<true>(bv.nodes[k], sc, pos, dir, ri, rf, h, panics, tc);
+    if (bv.root[k] != BVH_END) {
+      pr = make_prism_ray(bv, k, ri.dn);
+      bvh_walk<true>(bv.nodes[k], sc, pos, dir, ri, rf, pr, h, panics, tc);
+    }
   return h;
 }
 #endif

@@ -126,6 +126,23 @@ class Scene {
       check(rtx_scene_add_triangles(h_, &c, &m, 1), h_);
     }
   }
+  // Replaces object `index` (global insertion order) in place by an object of the SAME shape kind — what
+  // mutating a shape behind its Arc<Mutex<…>> (object.rs:12) does in the reference.  Only that record is
+  // re-uploaded and the LBVH is refitted instead of rebuilt (rtx_scene_update_*).
+  void update_object(uint64_t index, const object::Object& o) {
+    rtx_material m = o.material.c();
+    if (auto* s = std::get_if<object::Sphere>(&o.shape)) {
+      rtx_sphere c{s->position.c(), s->radius};
+      check(rtx_scene_update_spheres(h_, &index, &c, &m, 1), h_);
+    } else if (auto* p = std::get_if<object::Plane>(&o.shape)) {
+      rtx_plane c{p->position.c(), p->normal.c()};
+      check(rtx_scene_update_planes(h_, &index, &c, &m, 1), h_);
+    } else {
+      const auto& t = std::get<object::Triangle>(o.shape);
+      rtx_triangle c{{t.vertices[0].c(), t.vertices[1].c(), t.vertices[2].c()}};
+      check(rtx_scene_update_triangles(h_, &index, &c, &m, 1), h_);
+    }
+  }
   // scene.rs:144-170 → img[y][x], row 0 = bottom.  `seed` is the one added parameter.
   std::vector<std::vector<Vector3>> render(size_t width, size_t height, uint64_t seed = 0, rtx_stats* stats = nullptr) {
     sync();

@@ -79,6 +79,26 @@ int main() {
   rtx_stats st2{};
   scene.render(64, 64, 1, &st2);
   EXPECT(st2.rays == 64 * 64 && st2.paths == 64 * 64);
+  // in-place update: moving the red sphere away changes the picture; moving it back restores every bit
+  scene.config = scene.config.with_max_bounces(8).with_rays_per_pixel(4);
+  scene.update_object(1, {Sphere{{6, 0, 3}, 1}, Material::make({0.9, 0.2, 0.2}, {0, 0, 0}, 1.0)});
+  auto moved = scene.render(320, 200, 1);
+  bool differs = false;
+  for (size_t y = 0; y < 200 && !differs; ++y)
+    for (size_t x = 0; x < 320; ++x)
+      if (!(moved[y][x] == img[y][x])) { differs = true; break; }
+  EXPECT(differs);
+  scene.update_object(1, {Sphere{{6, 0, 1}, 1}, Material::make({0.9, 0.2, 0.2}, {0, 0, 0}, 1.0)});
+  auto back = scene.render(320, 200, 1);
+  for (size_t y = 0; y < 200; ++y)
+    for (size_t x = 0; x < 320; ++x) EXPECT(back[y][x] == img[y][x]);
+  bool threw = false;
+  try {
+    scene.update_object(0, {Sphere{{0, 0, 0}, 1}, Material::mirror()});  // object 0 is the plane
+  } catch (const rtx::Error&) {
+    threw = true;
+  }
+  EXPECT(threw);
   std::printf("render ok: %llu rays, %.3f ms device, mean radiance %.5f\nALL OK\n", (unsigned long long)st.rays,
               st.device_ms, sum / (320.0 * 200 * 3));
   return 0;
