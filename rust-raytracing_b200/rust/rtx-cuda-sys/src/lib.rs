@@ -30,6 +30,9 @@ pub struct rtx_stats {
 }
 #[repr(C)] #[derive(Clone, Copy, Debug)] pub struct rtx_shard { pub index: u32, pub count: u32 }
 #[repr(C)] pub struct rtx_scene { _private: [u8; 0] }
+/// One per-type shape buffer of gpu_state.rs:53-77 (GpuSerialize wire format).
+#[repr(C)] #[derive(Clone, Copy, Debug)]
+pub struct rtx_wire_shape_buffer { pub object_type: *const c_char, pub shape_bytes: *const c_void, pub shape_count: u64 }
 
 const _: () = assert!(std::mem::size_of::<rtx_vec3>() == 24);
 const _: () = assert!(std::mem::size_of::<rtx_mat3>() == 72);
@@ -51,6 +54,15 @@ pub const RTX_FLAG_SAMPLE_QUEUE: u32 = 64;
 pub const RTX_PEER_HANDLE_BYTES: usize = 64;
 
 extern "C" {
+    pub fn rtx_wire_decode_camera(bytes: *const c_void, out: *mut rtx_camera) -> rtx_status;
+    pub fn rtx_wire_decode_config(bytes: *const c_void, out: *mut rtx_config) -> rtx_status;
+    pub fn rtx_wire_decode_objects(object_records: *const c_void, n_objects: u64, shape_buffers: *const rtx_wire_shape_buffer,
+                                   n_shape_buffers: u32, out_kinds: *mut u32, out_shapes: *mut rtx_triangle,
+                                   out_materials: *mut rtx_material) -> rtx_status;
+    pub fn rtx_scene_add_wire_objects(scene: *mut rtx_scene, object_records: *const c_void, n_objects: u64,
+                                      shape_buffers: *const rtx_wire_shape_buffer, n_shape_buffers: u32) -> rtx_status;
+    pub fn rtx_scene_set_wire_camera(scene: *mut rtx_scene, bytes: *const c_void) -> rtx_status;
+    pub fn rtx_scene_set_wire_config(scene: *mut rtx_scene, bytes: *const c_void) -> rtx_status;
     pub fn rtx_scene_update_spheres(scene: *mut rtx_scene, object_indices: *const u64, shapes: *const rtx_sphere, materials: *const rtx_material, n: u64) -> rtx_status;
     pub fn rtx_scene_update_planes(scene: *mut rtx_scene, object_indices: *const u64, shapes: *const rtx_plane, materials: *const rtx_material, n: u64) -> rtx_status;
     pub fn rtx_scene_update_triangles(scene: *mut rtx_scene, object_indices: *const u64, shapes: *const rtx_triangle, materials: *const rtx_material, n: u64) -> rtx_status;
