@@ -184,7 +184,12 @@ RTX_D void bvh_leaf_test(const SceneView& sc, uint32_t child, V3 pos, V3 dir, co
   }
 }
 
-// Near-first walk with a short per-thread stack of (child ref, entry bound).
+// Near-first walk with a per-thread stack of (child ref, entry bound), in "while-while" form for triangles: an
+// inner loop descends until the lane holds a TRIANGLE leaf (or has finished), so the lanes of a warp run the
+// FP32 box tests together and then meet for the expensive FP64 triangle tests instead of interleaving the two
+// (measured on C4: 10.9 ms single loop, 10.3 ms when every leaf is postponed, 10.8 ms in this form).  Sphere
+// leaves are cheap and are tested inside the inner loop: making lanes wait for them costs more than it saves
+// (C3: 261 ms inside the loop, 305 ms postponed).
 template <bool PRISM>
 RTX_D void bvh_walk(const WideNode* __restrict__ nodes, const SceneView& sc, V3 pos, V3 dir, const RayInv& ri,
                     const RayF32& rf, const PrismRay& pr, Hit& h, uint32_t* panics, TraversalCounters& tc) {
@@ -192,11 +197,30 @@ RTX_D void bvh_walk(const WideNode* __restrict__ nodes, const SceneView& sc, V3 
   float stack_t[128];
   int sp = 0;
   uint32_t cur = 0;  // root
+  bool done = false;
+  // pop the next entry that can still beat the best distance; sets done when the stack runs dry
+  auto pop = [&]() {
+    const float best_up = __double2float_ru(h.t);
+    for (;;) {
+      if (sp == 0) {
+        done = true;
+        return;
+      }
+      --sp;
+      if (!(stack_t[sp] > best_up)) break;
+    }
+    cur = stack_ref[sp];
+  };
   for (;;) {
-    if (cur & WIDE_LEAF) {
-      ++tc.prims;
-      bvh_leaf_test<PRISM>(sc, cur, pos, dir, ri, h, panics);
-    } else {
+    for (;;) {
+      if (cur & WIDE_LEAF) {
+        if (cur & WIDE_TRI) break;
+        ++tc.prims;
+        bvh_leaf_test<PRISM>(sc, cur, pos, dir, ri, h, panics);
+        pop();
+        if (done) return;
+        continue;
+      }
       const WideNode* nd = nodes + cur;
       const float4 q0 = __ldg(reinterpret_cast<const float4*>(nd));
       const float4 q1 = __ldg(reinterpret_cast<const float4*>(nd) + 1);
@@ -216,22 +240,19 @@ RTX_D void bvh_walk(const WideNode* __restrict__ nodes, const SceneView& sc, V3 
         stack_t[sp] = first0 ? t1 : t0;
         ++sp;
         cur = first0 ? q3.x : q3.y;
-        continue;
       } else if (v0) {
         cur = q3.x;
-        continue;
       } else if (v1) {
         cur = q3.y;
-        continue;
+      } else {
+        pop();
+        if (done) return;
       }
     }
-    // pop, dropping entries that can no longer beat the best distance
-    for (;;) {
-      if (sp == 0) return;
-      --sp;
-      if (!(stack_t[sp] > __double2float_ru(h.t))) break;
-    }
-    cur = stack_ref[sp];
+    ++tc.prims;
+    bvh_leaf_test<PRISM>(sc, cur, pos, dir, ri, h, panics);
+    pop();
+    if (done) return;
   }
 }
 
