@@ -26,10 +26,16 @@
 namespace rtx {
 
 constexpr int RENDER_BLOCK = 256;
+#ifndef RTX_BVH_BLOCKS_PER_SM
+#define RTX_BVH_BLOCKS_PER_SM 3
+#endif
+// LBVH walks wait on L2 most of the time (ncu: long_scoreboard is the top stall), so the LBVH instantiations
+// trade registers for resident warps.
+constexpr int BVH_BLOCKS_PER_SM = RTX_BVH_BLOCKS_PER_SM;
 constexpr uint32_t FULL = 0xFFFFFFFFu;
 
 template <bool SMEM_SCENE, bool USE_BVH>
-__global__ void __launch_bounds__(RENDER_BLOCK, 2) render_megakernel(const __grid_constant__ RenderParams p) {
+__global__ void __launch_bounds__(RENDER_BLOCK, USE_BVH ? BVH_BLOCKS_PER_SM : 2) render_megakernel(const __grid_constant__ RenderParams p) {
   extern __shared__ __align__(128) unsigned char smem_raw[];
   const unsigned char* base = p.scene_blob;
   if (SMEM_SCENE) {
@@ -224,7 +230,7 @@ cudaError_t launch_render(const RenderParams& p, int sm_count, cudaStream_t stre
   const size_t smem = use_smem ? (size_t)p.layout.bytes + 128 : 0;
   cudaError_t e = cudaMemsetAsync(p.work_counter, 0, sizeof(uint32_t), stream);
   if (e != cudaSuccess) return e;
-  int blocks_per_sm = 2;
+  const int blocks_per_sm = p.use_bvh ? BVH_BLOCKS_PER_SM : 2;
   const uint64_t total_work = (uint64_t)p.my_tiles * GRANS_PER_TILE;
   // persistent grid: a multiple of the SM count, never more warps than granules
   uint64_t want_blocks = (total_work + (RENDER_BLOCK / 32) - 1) / (RENDER_BLOCK / 32);
