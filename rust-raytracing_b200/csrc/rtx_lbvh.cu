@@ -294,11 +294,11 @@ __global__ void k_emit_wide(int m, const BvhNode* __restrict__ nodes, const uint
     for (int k = 0; k < 3; ++k) {
       w.lo0[k] = __double2float_rd(nodes[0].lo[k]);
       w.hi0[k] = __double2float_ru(nodes[0].hi[k]);
-      w.lo1[k] = CUDART_INF_F;
-      w.hi1[k] = -CUDART_INF_F;
+      w.lo1[k] = w.lo0[k];  // a one-primitive tree: the second slot repeats the first (testing a primitive twice
+      w.hi1[k] = w.hi0[k];  // changes nothing), so the walk never has to recognise an empty slot
     }
     w.c0 = child_ref(nodes, 0);
-    w.c1 = WIDE_NONE;
+    w.c1 = w.c0;
     w.pad[0] = w.pad[1] = 0;
     out[0] = w;
     return;

@@ -46,7 +46,6 @@ struct __align__(16) BvhNode {  // 64 B = four 128-bit loads
 // Traversal node: both children's boxes in f32, rounded OUTWARD from the padded f64 boxes, + child refs.
 // Child ref: bit 31 = leaf; leaf payload: bit 30 = triangle (else sphere), bits 0..29 = index in its array.
 constexpr uint32_t WIDE_LEAF = 0x80000000u, WIDE_TRI = 0x40000000u, WIDE_IDX = 0x3FFFFFFFu;
-constexpr uint32_t WIDE_NONE = 0x7FFFFFFFu;  // empty child slot
 struct __align__(16) WideNode {  // 64 B = four 128-bit loads
   float lo0[3], hi0[3];
   float lo1[3], hi1[3];
@@ -69,93 +68,104 @@ struct TraversalCounters {
   unsigned long long nodes, prims;
 };
 
-// Per-ray f32 interval data for the conservative slab test.  Axes with a negative direction are mirrored
-// (x -> -x), so every component behaves as d >= 0.  o_dn <= o <= o_up and inv_dn <= 1/|d| <= inv_up hold
-// rigorously (directed rounding), inv_dn is finite.
+// Per-ray f32 data for the conservative slab test: one FFMA per slab side.
+//   exact      t  = (x - o) / d                      x = a box coordinate (f32), o, d = the f64 ray
+//   computed   u  = rn(x * inv + c)                  inv = rn32(1/d),  c = -(o/d) -+ e  rounded away from o/d
+// With e >= 2^-21 |o/d| the errors of inv (2^-24 relative, hitting x*inv = t + o/d), of o/d and of c's rounding are
+// all inside e, and what is left is the FFMA's own rounding: t >= u_near - 2^-22 |u_near|, t <= u_far + 2^-22 |u_far|.
+// Since the entry parameter is the max of three such t and the exit the min, the same relative widening applied
+// once to the max / min gives rigorous bounds.  An axis the ray does not move along (1/d or o/d not
+// representable, or NaN) gets inv = 0, c = -+inf: its slab never excludes anything.
 struct RayF32 {
-  float o_dn[3], o_up[3], inv_dn[3], inv_up[3];
+  float inv[3], cn[3], cf[3];
   bool neg[3];
 };
+constexpr float SLAB_REL = 2.384185791015625e-07f;  // 2^-22
 RTX_D RayF32 make_ray_f32(V3 pos, V3 dn) {
   RayF32 r;
   const double p[3] = {pos.x, pos.y, pos.z}, d[3] = {dn.x, dn.y, dn.z};
 #pragma unroll
   for (int k = 0; k < 3; ++k) {
     r.neg[k] = d[k] < 0.0;
-    const double o = r.neg[k] ? -p[k] : p[k];
-    r.o_dn[k] = __double2float_rd(o);
-    r.o_up[k] = __double2float_ru(o);
-    const double inv = 1.0 / fabs(d[k]);  // +inf for d == 0; correctly rounded, so widen by one f32 step each way
-    r.inv_dn[k] = fminf(__double2float_rd(inv * 0.99999999), 3.0e38f);
-    r.inv_up[k] = __double2float_ru(inv * 1.00000001);
+    const double inv = 1.0 / d[k];
+    const double oi = p[k] * inv;
+    if (fabs(inv) < 1.0e37 && fabs(oi) < 1.0e37) {
+      const double e = fabs(oi) * 4.76837158203125e-07 + 1.0e-30;  // 2^-21 |o/d|
+      r.inv[k] = __double2float_rn(inv);
+      r.cn[k] = __double2float_rd(-oi - e);
+      r.cf[k] = __double2float_ru(-oi + e);
+    } else {
+      r.inv[k] = 0.0f;
+      r.cn[k] = -CUDART_INF_F;
+      r.cf[k] = CUDART_INF_F;
+    }
   }
   return r;
 }
-// Lower bound of the entry parameter and upper bound of the exit parameter of one (mirrored) slab.
-RTX_D void slab(float lo, float hi, bool neg, float o_dn, float o_up, float inv_dn, float inv_up, float& tn, float& tf) {
-  const float l = neg ? -hi : lo, h = neg ? -lo : hi;
-  const float a = __fsub_rd(l, o_up);  // <= l - o
-  const float b = __fsub_ru(h, o_dn);  // >= h - o
-  tn = a < 0.0f ? __fmul_rd(a, inv_up) : __fmul_rd(a, inv_dn);
-  tf = b > 0.0f ? __fmul_ru(b, inv_up) : __fmul_ru(b, inv_dn);
+// Lower bound of the entry parameter (tn) and upper bound of the exit parameter (tf) of the slab of axis K.
+template <int K>
+RTX_D void slab(const float* lo, const float* hi, const RayF32& r, float& tn, float& tf) {
+  const float xn = r.neg[K] ? hi[K] : lo[K], xf = r.neg[K] ? lo[K] : hi[K];
+  tn = __fmaf_rn(xn, r.inv[K], r.cn[K]);
+  tf = __fmaf_rn(xf, r.inv[K], r.cf[K]);
+}
+// visit unless provably empty, provably behind the origin, or provably beyond the best distance
+RTX_D bool slab_verdict(float tn, float tf, float best_up, float& tnear) {
+  tnear = __fmaf_rn(-fabsf(tn), SLAB_REL, tn);
+  const float tfar = __fmaf_rn(fabsf(tf), SLAB_REL, tf);
+  return !(tfar < fmaxf(tnear, 0.0f)) && !(tnear > best_up);
 }
 RTX_D bool box_test(const float* lo, const float* hi, const RayF32& r, float best_up, float& tnear) {
   float tn0, tf0, tn1, tf1, tn2, tf2;
-  slab(lo[0], hi[0], r.neg[0], r.o_dn[0], r.o_up[0], r.inv_dn[0], r.inv_up[0], tn0, tf0);
-  slab(lo[1], hi[1], r.neg[1], r.o_dn[1], r.o_up[1], r.inv_dn[1], r.inv_up[1], tn1, tf1);
-  slab(lo[2], hi[2], r.neg[2], r.o_dn[2], r.o_up[2], r.inv_dn[2], r.inv_up[2], tn2, tf2);
-  tnear = fmaxf(fmaxf(tn0, tn1), tn2);
-  const float tfar = fminf(fminf(tf0, tf1), tf2);
-  // visit unless provably empty, provably behind the origin, or provably beyond the best distance
-  return !(tfar < fmaxf(tnear, 0.0f)) && !(tnear > best_up);
+  slab<0>(lo, hi, r, tn0, tf0);
+  slab<1>(lo, hi, r, tn1, tf1);
+  slab<2>(lo, hi, r, tn2, tf2);
+  return slab_verdict(fmaxf(fmaxf(tn0, tn1), tn2), fminf(fminf(tf0, tf1), tf2), best_up, tnear);
 }
 
-// Per-ray constants of one prism tree (dropped axis a).
+// Per-ray constants of the prism tree that drops axis A: rigorous f32 enclosures of the origin, and the lower
+// bound `den` of |d.n| over the tree's triangles: |d_a|*Z - |d_perp|*S (<= 0: no bound).
 struct PrismRay {
-  int a, b, c;      // dropped axis, kept axes
-  float den;        // lower bound of |d.n| over the tree's triangles: |d_a|*Z - |d_perp|*S (<= 0: no bound)
-  float s, z;       // the tree's S and Z
-  bool sign_known;  // all n_a of one sign
+  float o_dn[3], o_up[3];
+  float den, s, z;
 };
-RTX_D PrismRay make_prism_ray(const BvhView& bv, int tree, V3 dn) {
+template <int A>
+RTX_D PrismRay make_prism_ray(const BvhView& bv, V3 pos, V3 dn) {
+  constexpr int B = (A + 1) % 3, C = (A + 2) % 3;
   PrismRay pr;
-  pr.a = tree - 1;
-  pr.b = (pr.a + 1) % 3;
-  pr.c = (pr.a + 2) % 3;
-  const double d[3] = {dn.x, dn.y, dn.z};
-  pr.s = bv.prism_s[tree];
-  pr.z = bv.prism_z[tree];
-  pr.sign_known = bv.prism_sign[tree] != 0;
-  const float da = __double2float_rd(fabs(d[pr.a]) * 0.999999);
-  const float dp = __double2float_ru(sqrt(d[pr.b] * d[pr.b] + d[pr.c] * d[pr.c]) * 1.000001);
+  const double p[3] = {pos.x, pos.y, pos.z}, d[3] = {dn.x, dn.y, dn.z};
+#pragma unroll
+  for (int k = 0; k < 3; ++k) pr.o_dn[k] = __double2float_rd(p[k]), pr.o_up[k] = __double2float_ru(p[k]);
+  pr.s = bv.prism_s[1 + A];
+  pr.z = bv.prism_z[1 + A];
+  const float da = __double2float_rd(fabs(d[A]) * 0.999999);
+  const float dp = __double2float_ru(sqrt(d[B] * d[B] + d[C] * d[C]) * 1.000001);
   pr.den = __fsub_rd(__fmul_rd(da, pr.z), __fmul_ru(dp, pr.s));
   return pr;
 }
-// Entry test of a prism-tree node: slabs on the kept axes, then bounds (A) and (B) above.  All roundings are
-// directed so that a node is only skipped when the exact-arithmetic statement holds with margin; the f64
-// quantities they bound (|t| as computed by triangle_distance, the reported point) differ from the exact ones
-// by ~1e-16 relative, far inside the 1e-6 margins and the 2^-20 box padding.
-RTX_D bool box_test_prism(const float* lo, const float* hi, const RayF32& r, const PrismRay& pr, float best_up, float& tnear) {
+// Entry test of a node of the prism tree that drops axis A: slabs on the kept axes, then bounds (A) and (B)
+// above.  All roundings are directed so that a node is only skipped when the exact-arithmetic statement holds
+// with margin; the f64 quantities they bound (|t| as computed by triangle_distance, the reported point) differ
+// from the exact ones by ~1e-16 relative, far inside the 1e-6 margins and the 2^-20 box padding.
+template <int A>
+RTX_D bool box_test_prism(const float* lo, const float* hi, const RayF32& r, const PrismRay& pr, float best_up,
+                          float& tnear) {
+  constexpr int B = (A + 1) % 3, C = (A + 2) % 3;
   float tnb, tfb, tnc, tfc;
-  slab(lo[pr.b], hi[pr.b], r.neg[pr.b], r.o_dn[pr.b], r.o_up[pr.b], r.inv_dn[pr.b], r.inv_up[pr.b], tnb, tfb);
-  slab(lo[pr.c], hi[pr.c], r.neg[pr.c], r.o_dn[pr.c], r.o_up[pr.c], r.inv_dn[pr.c], r.inv_up[pr.c], tnc, tfc);
-  tnear = fmaxf(tnb, tnc);
-  const float tfar = fminf(tfb, tfc);
-  if ((tfar < fmaxf(tnear, 0.0f)) || (tnear > best_up)) return false;
+  slab<B>(lo, hi, r, tnb, tfb);
+  slab<C>(lo, hi, r, tnc, tfc);
+  if (!slab_verdict(fmaxf(tnb, tnc), fminf(tfb, tfc), best_up, tnear)) return false;
   if (!(pr.den > 0.0f)) return true;
-  // mirrored coordinates (the ray travels towards + on every axis): box [l, h], origin in [o_dn, o_up]
-  const float lb = r.neg[pr.b] ? -hi[pr.b] : lo[pr.b], hb = r.neg[pr.b] ? -lo[pr.b] : hi[pr.b];
-  const float lc = r.neg[pr.c] ? -hi[pr.c] : lo[pr.c], hc = r.neg[pr.c] ? -lo[pr.c] : hi[pr.c];
-  const float la = r.neg[pr.a] ? -hi[pr.a] : lo[pr.a], ha = r.neg[pr.a] ? -lo[pr.a] : hi[pr.a];
-  const float db = fmaxf(__fsub_ru(hb, r.o_dn[pr.b]), __fsub_ru(r.o_up[pr.b], lb));  // >= max |v_b - p_b|
-  const float dc = fmaxf(__fsub_ru(hc, r.o_dn[pr.c]), __fsub_ru(r.o_up[pr.c], lc));
+  const float db = fmaxf(__fsub_ru(hi[B], pr.o_dn[B]), __fsub_ru(pr.o_up[B], lo[B]));  // >= max |v_b - p_b|
+  const float dc = fmaxf(__fsub_ru(hi[C], pr.o_dn[C]), __fsub_ru(pr.o_up[C], lo[C]));
   const float dperp = __fmul_ru(__fsqrt_ru(__fadd_ru(__fmul_ru(db, db), __fmul_ru(dc, dc))), 1.000001f);
   const float sd = __fmul_ru(pr.s, dperp);
-  // (A): wholly ahead along a, and far enough that the a-term decides the sign of n.(v0 - pos)
-  const float gap = __fsub_rd(la, r.o_up[pr.a]);
+  // (A): wholly ahead along a (in the direction the ray travels), and far enough that the a-term decides the
+  // sign of n.(v0 - pos)
+  const float gap = r.neg[A] ? __fsub_rd(pr.o_dn[A], hi[A]) : __fsub_rd(lo[A], pr.o_up[A]);
   if (gap > 0.0f && __fmul_rd(gap, pr.z) > sd) return false;
   // (B): upper bound of |t|
-  const float da = fmaxf(__fsub_ru(ha, r.o_dn[pr.a]), __fsub_ru(r.o_up[pr.a], la));
+  const float da = fmaxf(__fsub_ru(hi[A], pr.o_dn[A]), __fsub_ru(pr.o_up[A], lo[A]));
   const float u = __fmul_ru(__fdiv_ru(__fadd_ru(sd, da), pr.den), 1.00001f);
   return !(tnear > u);
 }
@@ -202,9 +212,12 @@ RTX_D bool bvh_pop(const uint32_t* stack_ref, const float* stack_t, int& sp, dou
   return true;
 }
 
-template <bool PRISM>
+// AXIS < 0: the 3-D tree; AXIS = 0..2: the prism tree that drops that axis.
+template <int AXIS>
 RTX_D void bvh_walk(const WideNode* __restrict__ nodes, const SceneView& sc, V3 pos, V3 dir, const RayInv& ri,
                     const RayF32& rf, const PrismRay& pr, Hit& h, uint32_t* panics, TraversalCounters& tc) {
+  constexpr bool PRISM = AXIS >= 0;
+  constexpr int PA = PRISM ? AXIS : 0;
   uint32_t stack_ref[128];
   float stack_t[128];
   int sp = 0;
@@ -228,8 +241,8 @@ RTX_D void bvh_walk(const WideNode* __restrict__ nodes, const SceneView& sc, V3 
       const float lo1[3] = {q1.z, q1.w, q2.x}, hi1[3] = {q2.y, q2.z, q2.w};
       const float best_up = __double2float_ru(h.t);
       float t0, t1;
-      const bool v0 = PRISM ? box_test_prism(lo0, hi0, rf, pr, best_up, t0) : box_test(lo0, hi0, rf, best_up, t0);
-      const bool v1 = PRISM ? box_test_prism(lo1, hi1, rf, pr, best_up, t1) : box_test(lo1, hi1, rf, best_up, t1);
+      const bool v0 = PRISM ? box_test_prism<PA>(lo0, hi0, rf, pr, best_up, t0) : box_test(lo0, hi0, rf, best_up, t0);
+      const bool v1 = PRISM ? box_test_prism<PA>(lo1, hi1, rf, pr, best_up, t1) : box_test(lo1, hi1, rf, best_up, t1);
       if (v0 && v1) {
         const bool first0 = t0 <= t1;
         // depth <= 64 key bits + 32 index bits (Karras: every level lengthens the common prefix), so 128 holds
@@ -268,14 +281,20 @@ RTX_D Hit closest_lbvh(const SceneView& sc, const BvhView& bv, V3 pos, V3 dir, u
   // slab parameters are in units of dn, like every distance the shapes return
   const RayF32 rf = make_ray_f32(pos, ri.dn);
   PrismRay pr;
-  pr.a = 0, pr.b = 1, pr.c = 2, pr.den = 0.0f, pr.s = 1.0f, pr.z = 0.0f, pr.sign_known = false;
-  if (bv.root[0] != BVH_END) bvh_walk<false>(bv.nodes[0], sc, pos, dir, ri, rf, pr, h, panics, tc);
-#pragma unroll 1
-  for (int k = 1; k < 4; ++k)
-    if (bv.root[k] != BVH_END) {
-      pr = make_prism_ray(bv, k, ri.dn);
-      bvh_walk<true>(bv.nodes[k], sc, pos, dir, ri, rf, pr, h, panics, tc);
-    }
+  pr.den = 0.0f, pr.s = 1.0f, pr.z = 0.0f;
+  if (bv.root[0] != BVH_END) bvh_walk<-1>(bv.nodes[0], sc, pos, dir, ri, rf, pr, h, panics, tc);
+  if (bv.root[1] != BVH_END) {
+    pr = make_prism_ray<0>(bv, pos, ri.dn);
+    bvh_walk<0>(bv.nodes[1], sc, pos, dir, ri, rf, pr, h, panics, tc);
+  }
+  if (bv.root[2] != BVH_END) {
+    pr = make_prism_ray<1>(bv, pos, ri.dn);
+    bvh_walk<1>(bv.nodes[2], sc, pos, dir, ri, rf, pr, h, panics, tc);
+  }
+  if (bv.root[3] != BVH_END) {
+    pr = make_prism_ray<2>(bv, pos, ri.dn);
+    bvh_walk<2>(bv.nodes[3], sc, pos, dir, ri, rf, pr, h, panics, tc);
+  }
   return h;
 }
 #endif

@@ -15,6 +15,24 @@ def _rays(rng, n, spread):
     return np.concatenate([pos, d], axis=1)
 
 
+def _awkward_rays(rng, n, spread):
+    """Rays the f32 slab test has to survive: axis-parallel and nearly axis-parallel directions (1/d not
+    representable or huge), origins far outside the scene, a NaN direction."""
+    r = _rays(rng, n, spread)
+    q = n // 8
+    for k in range(3):
+        r[k * q:(k + 1) * q, 3 + k] = 0.0                      # one zero component
+    r[3 * q:4 * q, 3:] = np.eye(3)[rng.integers(0, 3, q)] * rng.choice([-1.0, 1.0], (q, 1))  # axis-parallel
+    r[4 * q:5 * q, 3] = rng.uniform(-1e-12, 1e-12, q)          # almost zero component
+    r[5 * q:6 * q, 4] = rng.choice([-1.0, 1.0], q) * 1e-300    # 1/d overflows f32
+    r[6 * q:7 * q, :3] *= 1.0e6                                # far origins
+    d = r[:, 3:]
+    r[:, 3:] = d / np.linalg.norm(d, axis=1, keepdims=True)
+    r[-1, 3:] = np.nan
+    r[-2, :3] = np.nan
+    return r
+
+
 def _same(sc, rtx, rays):
     tb, ib = sc.debug_closest_object(rays, flags=rtx.RTX_ACCEL_BRUTE)
     tl, il = sc.debug_closest_object(rays, flags=rtx.RTX_ACCEL_LBVH)
@@ -119,9 +137,24 @@ def test_tiny_trees(rtx, gpu):
         sc = rtx.Scene(rtx.Config(), rtx.Camera((0, 0, 0), (1, 0, 0), 1.0))
         sc.add_spheres(rng.uniform(-3, 3, (n, 3)), rng.uniform(0.5, 1.5, n), _mats(n))
         _same(sc, rtx, _rays(rng, 5000, 5.0))
+        _same(sc, rtx, _awkward_rays(rng, 4000, 5.0))
     sc = rtx.Scene(rtx.Config(), rtx.Camera((0, 0, 0), (1, 0, 0), 1.0))
-    sc.add_triangles(_visible_triangles(rng, 1, spread=3.0), _mats(1))
+    sc.add_triangles(_visible_triangles(rng, 1, spread=3.0), _mats(1))  # one-primitive trees (3-D and prism)
     _same(sc, rtx, _rays(rng, 5000, 5.0))
+    _same(sc, rtx, _awkward_rays(rng, 4000, 5.0))
+
+
+def test_awkward_rays(rtx, gpu):
+    rng = np.random.default_rng(25)
+    sc = rtx.Scene(rtx.Config(), rtx.Camera((0, 0, 0), (1, 0, 0), 1.0))
+    sc.add_spheres(rng.uniform(-10, 10, (400, 3)), rng.uniform(0.1, 1.5, 400), _mats(400))
+    tris = _visible_triangles(rng, 400, spread=10.0)
+    tris[:50, [2, 5, 8]] = np.round(tris[:50, [2]])     # axis-aligned (flat boxes), integer heights
+    sc.add_triangles(tris, _mats(400))
+    rays = _awkward_rays(rng, 40000, 11.0)
+    rays[:2000, 2] = np.round(rays[:2000, 2])           # origins in the planes of the flat triangles
+    ids = _same(sc, rtx, rays)
+    assert (ids != rtx.MISS_ID).mean() > 0.2
 
 
 @pytest.mark.parametrize("which", ["spheres", "terrain"])
