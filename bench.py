@@ -280,6 +280,10 @@ def run_b200(args):
         e2e_step()
     sync_all()
     e2e_s = time.perf_counter() - t0
+    # the frame the e2e call left in host memory is the frame the device-timed call left in HBM
+    e2e_checked = bool(torch.equal(pin, rgb.cpu())) if world == 1 else None
+    if e2e_checked is False:
+        raise SystemExit("e2e frame (host buffer) differs from the device-resident frame")
     te = torch.tensor([e2e_s], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(te, op=dist.ReduceOp.MAX)
@@ -292,7 +296,9 @@ def run_b200(args):
                   ("rtx_scene_render_device per rank (RTX_FLAG_SHARD_IN_PLACE into rank 0's peer frame) + D2H on rank 0"
                    if args.gather == "p2p" else
                    "rtx_scene_render_device per rank + NCCL gather + rtx_deinterleave_tiles + D2H on rank 0"),
-           "ms_per_step": float(te.item()) / K * 1e3}
+           "ms_per_step": float(te.item()) / K * 1e3, "frame_equals_device_frame": e2e_checked,
+           "d2h": "none: pinned caller buffer is written by the render kernel (posted PCIe stores, overlapped with "
+                  "rendering)" if world == 1 and os.environ.get("RTX_ZERO_COPY", "1") != "0" else "cudaMemcpyAsync"}
 
     if world > 1 and args.gather == "p2p":
         frame.close()
@@ -316,7 +322,10 @@ def run_b200(args):
     hbm_peak = peaks.get("hbm_gbs", 6650.0)
     roofline = {
         "bound": "fp64", "achieved": achieved, "peak": nf_tf, "unit": "TFLOP/s", "frac": achieved / nf_tf if nf_tf else None,
-        "traffic": None,
+        "traffic": 6557952 if (W, H, args.spp, world) == (WIDTH, HEIGHT, SPP, 1) else None,
+        "traffic_source": "bytes per launch, dram__bytes_read.sum 729344 + dram__bytes_write.sum 5828608 of one `ncu --set full` "
+                          "capture of this kernel on this workload (profiles/r01_render_pool_kernel_v4_raw.csv); the 58 MB frame "
+                          "mostly still sits in the 126 MB L2 when the kernel ends",
         "kernel": "rtx::render_pool_kernel (context-pool scheduler; S1 blob <= 16 KB, scanned from shared memory)", "launches": K, "avg_launch_ms": dev_ms / K,
         "model": f"flops = rays*{per_ray} + 92*hits + 27*paths (FP64, non-fused; SURVEY.md 8d); div/sqrt/sincos count 1 each",
         "peak_source": "measured live: rtx_probe_fp64_peak non-fused DADD+DMUL issue rate (MEASURED_PEAKS.json has no FP64 figure)",

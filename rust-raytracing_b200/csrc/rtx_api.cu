@@ -4,7 +4,10 @@
 // raytracing/camera.rs (Camera::new / set_direction / to_*_space).  The hot path itself lives in
 // rtx_render.cu; nothing here computes a pixel on the CPU.
 #include <chrono>
+#include <cmath>
+#include <cstdlib>
 #include <cstring>
+#include <limits>
 
 #include "rtx_internal.h"
 #include "rtx_trace.cuh"
@@ -84,6 +87,24 @@ static cudaError_t upload_touched(unsigned char* d_base, const std::vector<T>& h
   return e;
 }
 
+// f32 copy of the sphere records for the scan's conservative cull (rtx_trace.cuh, SphereCull) and the scene-wide
+// bounds its error margin is built from.  Rounded to nearest; the bounds are rounded up.
+static void build_sphere_cull(const std::vector<double>& sph, std::vector<float>& out, float* cmax, float* r2max) {
+  out.resize(sph.size());
+  double c = 0.0, r2 = 0.0;
+  bool finite = true;
+  for (size_t i = 0; i < sph.size(); ++i) {
+    out[i] = (float)sph[i];
+    finite = finite && std::isfinite(sph[i]);
+    const double a = std::fabs(sph[i]);
+    if ((i % SPH_STRIDE) == 3) r2 = a > r2 ? a : r2;
+    else c = a > c ? a : c;
+  }
+  const float inf = std::numeric_limits<float>::infinity();
+  *cmax = finite ? std::nextafterf((float)c, inf) : inf;
+  *r2max = finite ? std::nextafterf((float)r2, inf) : inf;
+}
+
 rtx_status ensure_uploaded(rtx_scene* s, cudaStream_t stream) {
   if (!s->dirty && s->d_blob) {
     const bool any = !s->upd_sph.empty() || !s->upd_pl.empty() || !s->upd_tri.empty() || !s->upd_mat.empty();
@@ -92,6 +113,11 @@ rtx_status ensure_uploaded(rtx_scene* s, cudaStream_t stream) {
     if (s->d_tri_raw && !s->upd_tri.empty()) {  // the LBVH's vertex copy follows the same updates
       std::vector<uint32_t> t = s->upd_tri;
       RTX_CUDA_TRY(s, upload_touched(reinterpret_cast<unsigned char*>(s->d_tri_raw), s->tri_raw, 9, t, stream));
+    }
+    if (!s->upd_sph.empty()) {
+      std::vector<uint32_t> t = s->upd_sph;
+      build_sphere_cull(s->sph, s->sph32, &s->layout.sph_cmax, &s->layout.sph_r2max);
+      RTX_CUDA_TRY(s, upload_touched(s->d_blob + L.off_sph32, s->sph32, SPH_STRIDE, t, stream));
     }
     RTX_CUDA_TRY(s, upload_touched(s->d_blob + L.off_sph, s->sph, SPH_STRIDE, s->upd_sph, stream));
     RTX_CUDA_TRY(s, upload_touched(s->d_blob + L.off_pl, s->pl, PL_STRIDE, s->upd_pl, stream));
@@ -114,6 +140,8 @@ rtx_status ensure_uploaded(rtx_scene* s, cudaStream_t stream) {
   L.off_sph_id = align16(off), off = L.off_sph_id + s->sph_id.size() * 4;
   L.off_pl_id = align16(off), off = L.off_pl_id + s->pl_id.size() * 4;
   L.off_tri_id = align16(off), off = L.off_tri_id + s->tri_id.size() * 4;
+  build_sphere_cull(s->sph, s->sph32, &L.sph_cmax, &L.sph_r2max);
+  L.off_sph32 = align16(off), off = L.off_sph32 + s->sph32.size() * 4;
   if (off > 0xFFFFFFF0ull) return fail(s, RTX_ERR_INVALID_ARGUMENT, "scene larger than 4 GiB is not supported");
   L.bytes = align16(off);
   if (L.bytes == 0) L.bytes = 16;
@@ -128,6 +156,7 @@ rtx_status ensure_uploaded(rtx_scene* s, cudaStream_t stream) {
   put(L.off_sph_id, s->sph_id.data(), s->sph_id.size() * 4);
   put(L.off_pl_id, s->pl_id.data(), s->pl_id.size() * 4);
   put(L.off_tri_id, s->tri_id.data(), s->tri_id.size() * 4);
+  put(L.off_sph32, s->sph32.data(), s->sph32.size() * 4);
   RTX_CUDA_TRY(s, grow(&s->d_blob, &s->d_blob_cap, L.bytes));
   // pageable source: the runtime stages it before returning, so `blob` may die at scope exit
   RTX_CUDA_TRY(s, cudaMemcpyAsync(s->d_blob, blob.data(), L.bytes, cudaMemcpyHostToDevice, stream));
@@ -220,6 +249,20 @@ uint32_t choose_accel(const rtx_scene* s, uint32_t flags) {
   if (a == RTX_ACCEL_BRUTE) return RTX_ACCEL_BRUTE;
   if (a == RTX_ACCEL_LBVH) return RTX_ACCEL_LBVH;
   return boxed > 48 ? RTX_ACCEL_LBVH : RTX_ACCEL_BRUTE;
+}
+
+// The device-side alias of a host pointer when the allocation is pinned and mapped (zero-copy), else null.
+template <typename T>
+static T* mapped_device_pointer(T* host) {
+  static const bool enabled = [] { const char* v = getenv("RTX_ZERO_COPY"); return !v || atoi(v) != 0; }();
+  if (!enabled || !host) return nullptr;
+  cudaPointerAttributes a{};
+  if (cudaPointerGetAttributes(&a, host) != cudaSuccess) {
+    cudaGetLastError();
+    return nullptr;
+  }
+  if (a.type != cudaMemoryTypeHost || !a.devicePointer) return nullptr;
+  return static_cast<T*>(a.devicePointer);
 }
 
 // Fills RenderParams and launches.  Counters / outputs are device pointers.
@@ -664,20 +707,32 @@ rtx_status rtx_scene_render(rtx_scene* s, uint32_t width, uint32_t height, uint6
   std::lock_guard<std::mutex> lk(s->mu);
   RTX_CUDA_TRY(s, cudaSetDevice(s->device));
   const size_t npix = (size_t)width * height;
-  if (want_rgb) RTX_CUDA_TRY(s, grow(&s->d_rgb, &s->d_rgb_cap, npix * 3 * sizeof(double)));
-  if (out_primary_hit_id) RTX_CUDA_TRY(s, grow(&s->d_ids, &s->d_ids_cap, npix * sizeof(uint32_t)));
+  // A caller buffer in pinned, device-mapped host memory (rtx_host_alloc, cudaHostAlloc, cudaHostRegister) is
+  // written by the render kernel itself: every finished pixel is a posted store over PCIe while the rest of the
+  // frame is still rendering, so there is no device frame and no copy after the kernel (RTX_ZERO_COPY=0 turns it
+  // off).  Pageable buffers go through the scene's device frame + cudaMemcpyAsync.
+  double* k_rgb = want_rgb ? mapped_device_pointer(out_rgb) : nullptr;
+  uint32_t* k_ids = out_primary_hit_id ? mapped_device_pointer(out_primary_hit_id) : nullptr;
+  const bool copy_rgb = want_rgb && !k_rgb, copy_ids = out_primary_hit_id && !k_ids;
+  if (copy_rgb) {
+    RTX_CUDA_TRY(s, grow(&s->d_rgb, &s->d_rgb_cap, npix * 3 * sizeof(double)));
+    k_rgb = s->d_rgb;
+  }
+  if (copy_ids) {
+    RTX_CUDA_TRY(s, grow(&s->d_ids, &s->d_ids_cap, npix * sizeof(uint32_t)));
+    k_ids = s->d_ids;
+  }
   RTX_CUDA_TRY(s, cudaMemsetAsync(s->d_counters, 0, 8 * sizeof(unsigned long long), s->stream));
   uint32_t launches = 0;
   const bool had_bvh = s->bvh_valid;
   RTX_CUDA_TRY(s, cudaEventRecord(s->ev0, s->stream));
-  rtx_status st = render_common(s, width, height, seed, flags, nullptr, want_rgb ? s->d_rgb : nullptr,
-                                out_primary_hit_id ? s->d_ids : nullptr, s->d_counters, s->d_work_counter, s->stream,
-                                &launches);
+  rtx_status st = render_common(s, width, height, seed, flags, nullptr, k_rgb, k_ids, s->d_counters, s->d_work_counter,
+                                s->stream, &launches);
   if (st != RTX_OK) return st;
   RTX_CUDA_TRY(s, cudaEventRecord(s->ev1, s->stream));
-  if (want_rgb)
+  if (copy_rgb)
     RTX_CUDA_TRY(s, cudaMemcpyAsync(out_rgb, s->d_rgb, npix * 3 * sizeof(double), cudaMemcpyDeviceToHost, s->stream));
-  if (out_primary_hit_id)
+  if (copy_ids)
     RTX_CUDA_TRY(s, cudaMemcpyAsync(out_primary_hit_id, s->d_ids, npix * sizeof(uint32_t), cudaMemcpyDeviceToHost,
                                     s->stream));
   unsigned long long counters[8] = {0, 0, 0, 0, 0, 0, 0, 0};

@@ -21,6 +21,7 @@ struct rtx_scene {
   // host-side packed records (see rtx_scene.cuh); object index = insertion order across all three
   std::vector<double> sph, pl, tri, mat;
   std::vector<uint32_t> sph_id, pl_id, tri_id;
+  std::vector<float> sph32;     // f32 copy of `sph` for the scan's conservative cull (rebuilt at upload)
   std::vector<double> tri_raw;  // 9 doubles per triangle: the LBVH builder needs the vertices for boxes
   std::vector<uint32_t> obj_ref;  // per object: REF_* | index within its shape array
   uint64_t n_obj = 0;

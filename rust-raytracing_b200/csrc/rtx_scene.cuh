@@ -41,7 +41,11 @@ struct SceneLayout {
   uint32_t n_obj, n_sph, n_pl, n_tri;
   uint32_t off_sph, off_pl, off_tri, off_mat;
   uint32_t off_sph_id, off_pl_id, off_tri_id;
+  uint32_t off_sph32;  // float4 per sphere (cx, cy, cz, r*r rounded to f32): conservative cull of the scan only
   uint32_t bytes;  // total blob size, multiple of 16
+  // Scene-wide bounds for the f32 cull (rtx_trace.cuh, SphereCull): max |centre component| and max r*r over
+  // all spheres, rounded up; +inf when a sphere is not finite (then nothing is ever culled).
+  float sph_cmax, sph_r2max;
 };
 
 struct SceneView {
@@ -52,6 +56,8 @@ struct SceneView {
   const uint32_t* sph_id;
   const uint32_t* pl_id;
   const uint32_t* tri_id;
+  const float* sph32;
+  float sph_cmax, sph_r2max;
   uint32_t n_obj, n_sph, n_pl, n_tri;
 };
 
@@ -64,6 +70,9 @@ RTX_HD SceneView make_view(const unsigned char* base, const SceneLayout& L) {
   v.sph_id = reinterpret_cast<const uint32_t*>(base + L.off_sph_id);
   v.pl_id = reinterpret_cast<const uint32_t*>(base + L.off_pl_id);
   v.tri_id = reinterpret_cast<const uint32_t*>(base + L.off_tri_id);
+  v.sph32 = reinterpret_cast<const float*>(base + L.off_sph32);
+  v.sph_cmax = L.sph_cmax;
+  v.sph_r2max = L.sph_r2max;
   v.n_obj = L.n_obj;
   v.n_sph = L.n_sph;
   v.n_pl = L.n_pl;

@@ -206,6 +206,45 @@ RTX_D bool triangle_distance(const double* __restrict__ rec, V3 pos, V3 dir, con
   return false;
 }
 
+// Conservative f32 cull for the sphere scan.  It never decides a hit: a sphere it lets through is evaluated by
+// sphere_candidate/sphere_root in f64 exactly as before; a sphere it rejects is one that sphere_candidate is
+// *proven* to reject (q <= 0 or h >= 0), so the scan's result is unchanged bit for bit.
+//   f32 values: o32 = p32 - c32, h32 = o32·d32, c32 = o32·o32 - r2_32, q32 = h32² - a32·c32 (FMA, round to nearest).
+//   With u = 2^-24, R >= |p_i| + |c_i| for every component and sphere, D1 = |d_x|+|d_y|+|d_z|:
+//     |o32_i - o_i| <= 2uR, |h32 - h| <= 6u·R·D1, |c32 - c| <= 25uR² + 2u·r², and
+//     |q32 - q| <= 14u·B with B = (R·D1)² + a(3R² + r²max)   (conversion + one rounding per operation;
+//   the f64 roundings of the exact path, ~2^-53·B, disappear in the slack).  Margins used: 32u·B for q and 16u·R·D1
+//   for h, plus 1e-30 absolute for f32 underflow.  NaN anywhere makes a comparison false ⇒ "keep"; B >= 1e37
+//   (overflow range) switches the cull off for the ray.
+struct SphereCull {
+  float px, py, pz, dx, dy, dz, a, neg_mq, mh;
+};
+RTX_D SphereCull sphere_cull_setup(const SceneView& sc, V3 pos, const RayInv& ri) {
+  SphereCull k;
+  k.px = __double2float_rn(pos.x), k.py = __double2float_rn(pos.y), k.pz = __double2float_rn(pos.z);
+  k.dx = __double2float_rn(ri.dn.x), k.dy = __double2float_rn(ri.dn.y), k.dz = __double2float_rn(ri.dn.z);
+  k.a = __double2float_ru(ri.a);
+  const float pmax = fmaxf(fmaxf(fabsf(k.px), fabsf(k.py)), fabsf(k.pz));
+  const float R = __fadd_ru(pmax, sc.sph_cmax);
+  const float rd = __fmul_ru(R, __fadd_ru(__fadd_ru(fabsf(k.dx), fabsf(k.dy)), fabsf(k.dz)));
+  const float B = __fmaf_ru(rd, rd, __fmul_ru(fabsf(k.a), __fmaf_ru(__fmul_ru(3.0f, R), R, sc.sph_r2max)));
+  // B far from the f32 range: no intermediate of sphere_cull_keep can overflow to an infinity that would
+  // compare as a certain miss.  Otherwise (or NaN) the margins are NaN and every sphere is kept.
+  const bool ok = B < 1e37f;
+  k.neg_mq = ok ? -__fmaf_ru(B, 1.9073486328125e-6f /* 2^-19 */, 1e-30f) : CUDART_NAN_F;
+  k.mh = ok ? __fmaf_ru(rd, 9.5367431640625e-7f /* 2^-20 */, 1e-30f) : CUDART_NAN_F;
+  return k;
+}
+// false only when sphere_candidate is certain to return false for this sphere
+RTX_D bool sphere_cull_keep(const float* __restrict__ rec32, const SphereCull& k) {
+  const float4 s = *reinterpret_cast<const float4*>(rec32);
+  const float ox = k.px - s.x, oy = k.py - s.y, oz = k.pz - s.z;
+  const float h = fmaf(oz, k.dz, fmaf(oy, k.dy, ox * k.dx));
+  const float c = fmaf(oz, oz, fmaf(oy, oy, fmaf(ox, ox, -s.w)));
+  const float q = fmaf(h, h, -(k.a * c));
+  return !(q <= k.neg_mq) && !(h >= k.mh);
+}
+
 // scene.rs:243-251 — brute-force scan over all three shape arrays.
 RTX_D Hit closest_brute(const SceneView& sc, V3 pos, V3 dir, uint32_t* panics) {
   Hit h;
@@ -213,26 +252,24 @@ RTX_D Hit closest_brute(const SceneView& sc, V3 pos, V3 dir, uint32_t* panics) {
   h.id = MISS_ID;
   h.ref = 0;
   const RayInv ri = ray_invariants(dir);
-  // Spheres, in chunks of 32: a branch-free pass computes the discriminant/sign test of every sphere in the
-  // chunk and records the survivors as one bit each, so the compiler can overlap the FP64 chains of
-  // neighbouring spheres; the few survivors (usually 0-2 per ray) are then revisited — the same operations
-  // on the same values, so the same bits — for the sqrt + division of the root.  `consider` is a
-  // lexicographic (t, id) minimum, so the visiting order is irrelevant.
+  // Spheres, in chunks of 32: a branch-free f32 pass (SphereCull) records as one bit each the spheres that
+  // cannot be ruled out; those few (usually 0-2 per ray) then go through the exact f64 test and, if it passes,
+  // the sqrt + division of the root.  `consider` is a lexicographic (t, id) minimum, so the visiting order
+  // is irrelevant.
+  const SphereCull cull = sphere_cull_setup(sc, pos, ri);
   for (uint32_t base = 0; base < sc.n_sph; base += 32u) {
     const uint32_t cnt = min(32u, sc.n_sph - base);
     const double* __restrict__ chunk = sc.sph + (size_t)base * SPH_STRIDE;
+    const float* __restrict__ chunk32 = sc.sph32 + (size_t)base * SPH_STRIDE;
     uint32_t cand = 0u;
 #pragma unroll 2
-    for (uint32_t j = 0; j < cnt; ++j) {
-      double hh, qq;
-      cand |= (sphere_candidate(chunk + (size_t)j * SPH_STRIDE, pos, ri, &hh, &qq) ? 1u : 0u) << j;
-    }
+    for (uint32_t j = 0; j < cnt; ++j) cand |= (sphere_cull_keep(chunk32 + (size_t)j * SPH_STRIDE, cull) ? 1u : 0u) << j;
     while (cand != 0u) {
       const uint32_t j = (uint32_t)__ffs((int)cand) - 1u;
       cand &= cand - 1u;
       double hh, qq;
-      sphere_candidate(chunk + (size_t)j * SPH_STRIDE, pos, ri, &hh, &qq);
-      consider(h, sphere_root(hh, qq, ri), sc.sph_id[base + j], REF_SPHERE | (base + j));
+      if (sphere_candidate(chunk + (size_t)j * SPH_STRIDE, pos, ri, &hh, &qq))
+        consider(h, sphere_root(hh, qq, ri), sc.sph_id[base + j], REF_SPHERE | (base + j));
     }
   }
   for (uint32_t i = 0; i < sc.n_pl; ++i) {

@@ -208,3 +208,56 @@ def test_context_pool_kernel_equals_lane_kernel(rtx, gpu):
             assert c.tobytes() == b.tobytes() and np.array_equal(ic, ib) and sq == sb, (w, h, q, sq, sb)
     a = empty.render(33, 9, seed=1)
     assert not a.any()
+
+
+def test_pinned_host_buffers_are_written_by_the_kernel(rtx, gpu):
+    """rtx_scene_render with pinned, device-mapped caller buffers stores pixels from the render kernel itself
+    (no device frame, no D2H copy); pageable buffers go through the device frame.  Same bytes either way — pool
+    kernel with both queues, lane kernel, LBVH, ids-only."""
+    import torch
+    from rtx_b200 import scenes
+    cases = [(scenes.sphere_demo(rays_per_pixel=8, max_bounces=8), 333, 177, rtx.RTX_ACCEL_AUTO),
+             (scenes.sphere_demo(rays_per_pixel=8, max_bounces=8), 333, 177, rtx.RTX_FLAG_SAMPLE_QUEUE),
+             (scenes.sphere_demo(rays_per_pixel=2, max_bounces=3), 200, 90, rtx.RTX_FLAG_LANE_KERNEL),
+             (scenes.random_spheres(n=500, rays_per_pixel=2, max_bounces=4), 240, 135, rtx.RTX_ACCEL_LBVH)]
+    for sc, w, h, fl in cases:
+        a, ia = sc.render(w, h, seed=9, flags=fl, want_ids=True)  # numpy: pageable
+        pin = torch.full((h, w, 3), -1.0, dtype=torch.float64).pin_memory()
+        pin_ids = torch.full((h, w), 12345, dtype=torch.int32).pin_memory()
+        b, ib = sc.render(w, h, seed=9, flags=fl, out=pin.numpy(), out_ids=pin_ids.numpy().view(np.uint32))
+        assert a.tobytes() == b.tobytes() and np.array_equal(ia, ib), (w, h, fl)
+        ids_only = torch.full((h, w), 12345, dtype=torch.int32).pin_memory()
+        st = rtx.Stats()
+        hnd = sc._sync()
+        import ctypes as C
+        rtx._abi.check(rtx._abi.load().rtx_scene_render(hnd, w, h, 9, fl | rtx.RTX_FLAG_NO_RADIANCE, None,
+                                                        ids_only.numpy().ctypes.data, C.byref(st)), hnd)
+        assert np.array_equal(ids_only.numpy().view(np.uint32), ia)
+
+
+def test_f32_sphere_cull_is_conservative(rtx, oracle, gpu):
+    """The scan's f32 pre-test (rtx_trace.cuh, SphereCull) may only drop spheres the exact f64 test drops.  Scenes
+    built to stress its error margin: grazing rays, huge and tiny coordinates, a camera far from the spheres,
+    spheres at 1e19 (f32 overflow range of the squared terms) and 1e-25 (f32 underflow), a non-finite sphere."""
+    from rtx_b200 import Camera, Config, Material, Object, Scene, Sphere
+    def build(scale, cam_dist, extra=None):
+        sc = Scene(Config().with_rays_per_pixel(2).with_max_bounces(3),
+                   Camera((-cam_dist * scale, 0.1 * scale, 0.2 * scale), (1, 0, 0), 0.02 if cam_dist > 100 else 1.0))
+        for i, (x, y, z, r) in enumerate([(6, 0, 1, 1), (6, 2.0000001, 1, 1), (9, -1, 0.5, 1.5), (4, 1, -0.2, 0.25),
+                                          (12, 0, 6, 3), (7, -3, 2, 0.999999)]):
+            m = Material.light((2, 2, 2)) if i == 4 else Material((0.8, 0.5 + 0.05 * i, 0.3), (0, 0, 0), 0.3 * (i % 3))
+            sc.add_object(Object(Sphere((x * scale, y * scale, z * scale), r * scale), m))
+        if extra:
+            sc.add_object(Object(Sphere(*extra), Material.colored((0.5, 0.5, 0.5))))
+        return sc
+    cases = [build(1.0, 0), build(1e6, 0), build(1e-6, 0), build(1.0, 5000.0), build(1e19, 0), build(1e-25, 0),
+             build(1.0, 0, ((float("inf"), 0.0, 0.0), 1.0)), build(1.0, 0, ((3e38, 0.0, 0.0), 1.0)),
+             build(1.0, 0, ((5.0, 0.0, float("nan")), 1.0))]
+    for k, sc in enumerate(cases):
+        rgb, ids = sc.render(160, 90, seed=3, flags=rtx.RTX_ACCEL_BRUTE, want_ids=True)
+        ref = oracle.render_scene(sc, 160, 90, seed=3)
+        assert np.array_equal(ids, ref["ids"]), k
+        assert rgb.tobytes() == ref["rgb"].tobytes(), k
+        assert sc.last_stats.rays == ref["rays"], k
+        if k in (0, 1, 2, 3, 4, 5):
+            assert (ids != 0xFFFFFFFF).any(), k  # the spheres are actually in view
