@@ -241,7 +241,9 @@ def test_f32_sphere_cull_is_conservative(rtx, oracle, gpu):
     spheres at 1e19 (f32 overflow range of the squared terms) and 1e-25 (f32 underflow), a non-finite sphere."""
     from rtx_b200 import Camera, Config, Material, Object, Scene, Sphere
     def build(scale, cam_dist, extra=None):
-        sc = Scene(Config().with_rays_per_pixel(2).with_max_bounces(3),
+        cfg = Config().with_rays_per_pixel(2).with_max_bounces(3)
+        cfg = cfg.with_focal_length(10.0 * scale).with_focal_offset(1e-4 * scale).with_non_focal_offset(1e-4 * scale)
+        sc = Scene(cfg,
                    Camera((-cam_dist * scale, 0.1 * scale, 0.2 * scale), (1, 0, 0), 0.02 if cam_dist > 100 else 1.0))
         for i, (x, y, z, r) in enumerate([(6, 0, 1, 1), (6, 2.0000001, 1, 1), (9, -1, 0.5, 1.5), (4, 1, -0.2, 0.25),
                                           (12, 0, 6, 3), (7, -3, 2, 0.999999)]):
@@ -261,3 +263,17 @@ def test_f32_sphere_cull_is_conservative(rtx, oracle, gpu):
         assert sc.last_stats.rays == ref["rays"], k
         if k in (0, 1, 2, 3, 4, 5):
             assert (ids != 0xFFFFFFFF).any(), k  # the spheres are actually in view
+
+
+def test_c2_full_size_frame_equals_oracle(rtx, oracle, gpu):
+    """BASELINE.json configs[1] at full size — S1, 1920x1080, 64 spp, max depth 8: every byte of the frame, every
+    primary hit id and the ray count equal the CPU oracle's (245 M rays; the oracle takes a few seconds on the
+    box's host threads)."""
+    from rtx_b200 import scenes
+    sc = scenes.sphere_demo(rays_per_pixel=64, max_bounces=8)
+    rgb, ids = sc.render(1920, 1080, seed=1, want_ids=True)
+    ref = oracle.render_scene(sc, 1920, 1080, seed=1)
+    assert np.array_equal(ids, ref["ids"])
+    assert sc.last_stats.rays == ref["rays"] == 245087388
+    assert float(np.abs(rgb - ref["rgb"]).max()) <= 1e-4 and psnr(rgb, ref["rgb"]) >= PSNR_MIN  # the north-star gates
+    assert rgb.tobytes() == ref["rgb"].tobytes()  # the bar this repo holds: bit-exact
