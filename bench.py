@@ -26,6 +26,13 @@ sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.join(ROOT, "rust-raytracing_b200"))
 
 WIDTH, HEIGHT, SPP, MAX_BOUNCES, SEED = 1920, 1080, 64, 8, 1
+# one `ncu --set full` capture of render_pool_kernel<64,1,true,24> on this workload (profiles/r01_render_pool_kernel_v6_raw.csv)
+NCU_TRAFFIC = 34150912 + 3167205000
+NCU_TRAFFIC_SOURCE = ("bytes per launch, dram__bytes_read.sum 34.2 MB + dram__bytes_write.sum 3167.2 MB of one `ncu --set full` capture of "
+                      "render_pool_kernel<64,1,true,24> on this workload (profiles/r01_render_pool_kernel_v6_raw.csv): the sample "
+                      "queue's scratch, 24 B per camera path x 132.7 M paths = 3185 MB, written once; tail_sum_kernel then reads "
+                      "it once (3185 MB in 0.45 ms = 7.07 TB/s, profiles/r01_tail_sum_kernel_raw.csv); the 49.8 MB frame itself "
+                      "is written by tail_sum_kernel")
 METRIC = "Mrays/s at 1080p 64spp, 1/2/4/8 B200, vs ref CPU path on host cores"
 WORKLOAD = "S1 sphere demo scene (1 plane + 6 spheres), 1920x1080, 64 spp, max depth 8 (BASELINE.json configs[1])"
 
@@ -313,7 +320,9 @@ def run_b200(args):
     flops, per_ray = algorithmic_flops(scene, rays, hits, paths)
     # at N > 1 dev_ms contains the gather; the kernel-only figure is quoted at N = 1
     achieved = flops / (dev_ms * 1e-3) / 1e12
-    hbm_bytes = K * npix * 28
+    per_rank = max(1, scene.last_device_launches)
+    sample_queue = per_rank >= 2  # (granule, sample) entries: 24 B of scratch per camera path, written then summed
+    hbm_bytes = K * npix * 28 + (paths * 48 if sample_queue else 0)
     peaks = {}
     try:
         peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
@@ -322,11 +331,12 @@ def run_b200(args):
     hbm_peak = peaks.get("hbm_gbs", 6650.0)
     roofline = {
         "bound": "fp64", "achieved": achieved, "peak": nf_tf, "unit": "TFLOP/s", "frac": achieved / nf_tf if nf_tf else None,
-        "traffic": 6557952 if (W, H, args.spp, world) == (WIDTH, HEIGHT, SPP, 1) else None,
-        "traffic_source": "bytes per launch, dram__bytes_read.sum 729344 + dram__bytes_write.sum 5828608 of one `ncu --set full` "
-                          "capture of this kernel on this workload (profiles/r01_render_pool_kernel_v4_raw.csv); the 58 MB frame "
-                          "mostly still sits in the 126 MB L2 when the kernel ends",
-        "kernel": "rtx::render_pool_kernel (context-pool scheduler; S1 blob <= 16 KB, scanned from shared memory)", "launches": K, "avg_launch_ms": dev_ms / K,
+        "traffic": NCU_TRAFFIC if (W, H, args.spp, world) == (WIDTH, HEIGHT, SPP, 1) and sample_queue else None,
+        "traffic_source": NCU_TRAFFIC_SOURCE,
+        "kernel": "rtx::render_pool_kernel (context-pool scheduler; S1 blob <= 16 KB, scanned from shared memory)" +
+                  (" + rtx::tail_sum_kernel (ordered per-pixel sum of the sample queue's scratch, ~4 % of the step): the "
+                   "events bracket both, so `achieved` is a lower bound for the render kernel alone" if sample_queue else ""),
+        "launches": K * per_rank, "avg_launch_ms": dev_ms / K,
         "model": f"flops = rays*{per_ray} + 92*hits + 27*paths (FP64, non-fused; SURVEY.md 8d); div/sqrt/sincos count 1 each",
         "peak_source": "measured live: rtx_probe_fp64_peak non-fused DADD+DMUL issue rate (MEASURED_PEAKS.json has no FP64 figure)",
         "fp64_fma_peak_tflops": fma_tf,
@@ -340,8 +350,10 @@ def run_b200(args):
         cpu_baseline = cpu_render_rate(W, H, args.cpu_seconds)
         for k in ("seconds", "rays", "spp"):
             cpu_baseline.pop(k)
-    # render kernel per rank (+ de-interleave on rank 0 with --gather nccl); NCCL's kernels are not ours
-    launches_per_step = world if (world == 1 or args.gather == "p2p") else world + 1
+    # our kernels per step: what rtx_scene_render_device launched on a rank (render kernel; + the ordered-sum pass
+    # under the sample queue) x ranks, + de-interleave on rank 0 with --gather nccl; NCCL's kernels are not ours
+    per_rank = max(1, scene.last_device_launches)
+    launches_per_step = world * per_rank if (world == 1 or args.gather == "p2p") else world * per_rank + 1
     print(json.dumps({
         "metric": METRIC, "value": value, "unit": "Mrays/s", "n_gpus": world, "steps": K, "warmup": WU,
         "ms_per_step": dev_ms / K, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,

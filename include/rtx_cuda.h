@@ -149,6 +149,8 @@ rtx_status rtx_scene_rebuild_accel(rtx_scene* scene);
 /* Number of LBVH refits / full builds this scene has performed (statistics; tests). */
 uint32_t   rtx_scene_accel_refits(const rtx_scene* scene);
 uint32_t   rtx_scene_accel_builds(const rtx_scene* scene);
+/* Kernels the most recent rtx_scene_render_device call on this scene launched (statistics; bench.py). */
+uint32_t   rtx_scene_last_launches(const rtx_scene* scene);
 uint64_t   rtx_scene_object_count(const rtx_scene* scene);
 
 /* ---- render -------------------------------------------------------------------------------- */

@@ -269,7 +269,7 @@ static T* mapped_device_pointer(T* host) {
 static rtx_status render_common(rtx_scene* s, uint32_t width, uint32_t height, uint64_t seed, uint32_t flags,
                                 const rtx_shard* shard, double* d_rgb, uint32_t* d_ids,
                                 unsigned long long* d_counters, uint32_t* d_work_counter, cudaStream_t stream,
-                                uint32_t* launches) {
+                                uint32_t* launches, bool rgb_is_host = false) {
   if (width == 0 || height == 0) return fail(s, RTX_ERR_INVALID_ARGUMENT, "width and height must be non-zero");
   if ((uint64_t)width * height > 0xFFFFFFFFull) return fail(s, RTX_ERR_INVALID_ARGUMENT, "image too large");
   const uint32_t accel = flags & RTX_ACCEL_MASK;
@@ -316,6 +316,7 @@ static rtx_status render_common(rtx_scene* s, uint32_t width, uint32_t height, u
   p.work_counter = d_work_counter;
   p.out_rgb = (flags & RTX_FLAG_NO_RADIANCE) ? nullptr : d_rgb;
   p.out_ids = d_ids;
+  p.out_is_host = rgb_is_host ? 1u : 0u;
   p.ray_counter = d_counters;
   if (p.my_tiles == 0) return RTX_OK;
   p.tail_first = p.my_tiles * GRANS_PER_TILE, p.tail_granules = 0, p.tail_scratch = nullptr, p.tail_done = nullptr;
@@ -663,6 +664,7 @@ rtx_status rtx_scene_rebuild_accel(rtx_scene* s) {
 
 uint32_t rtx_scene_accel_refits(const rtx_scene* s) { return s ? s->bvh_refits : 0; }
 uint32_t rtx_scene_accel_builds(const rtx_scene* s) { return s ? s->bvh_builds : 0; }
+uint32_t rtx_scene_last_launches(const rtx_scene* s) { return s ? s->last_launches : 0; }
 
 rtx_status rtx_scene_clear_objects(rtx_scene* s) {
   if (!s) return fail(s, RTX_ERR_INVALID_ARGUMENT, "null scene");
@@ -693,8 +695,10 @@ rtx_status rtx_scene_render_device(rtx_scene* s, uint32_t width, uint32_t height
   static thread_local uint32_t slot = 0;
   uint32_t* wc = s->d_work_counter + (slot++ & 63u);
   uint32_t launches = 0;
-  return render_common(s, width, height, seed, flags, shard, (double*)d_out_rgb, (uint32_t*)d_out_primary_hit_id,
-                       (unsigned long long*)d_out_counters, wc, (cudaStream_t)cuda_stream, &launches);
+  const rtx_status st = render_common(s, width, height, seed, flags, shard, (double*)d_out_rgb, (uint32_t*)d_out_primary_hit_id,
+                                      (unsigned long long*)d_out_counters, wc, (cudaStream_t)cuda_stream, &launches);
+  s->last_launches = launches;
+  return st;
 }
 
 rtx_status rtx_scene_render(rtx_scene* s, uint32_t width, uint32_t height, uint64_t seed, uint32_t flags,
@@ -727,7 +731,7 @@ rtx_status rtx_scene_render(rtx_scene* s, uint32_t width, uint32_t height, uint6
   const bool had_bvh = s->bvh_valid;
   RTX_CUDA_TRY(s, cudaEventRecord(s->ev0, s->stream));
   rtx_status st = render_common(s, width, height, seed, flags, nullptr, k_rgb, k_ids, s->d_counters, s->d_work_counter,
-                                s->stream, &launches);
+                                s->stream, &launches, want_rgb && !copy_rgb);
   if (st != RTX_OK) return st;
   RTX_CUDA_TRY(s, cudaEventRecord(s->ev1, s->stream));
   if (copy_rgb)

@@ -42,6 +42,7 @@ struct rtx_scene {
   bool bvh_valid = false;
   bool bvh_refit = false;   // primitives moved since the trees were built/refitted: same hierarchy, new boxes
   uint32_t bvh_refits = 0, bvh_builds = 0;  // refits / full builds performed (statistics)
+  uint32_t last_launches = 0;               // kernels launched by the most recent rtx_scene_render_device
   // what a refit needs of each tree: its primitive list, validity, sorted order and hierarchy
   struct TreeTopo {
     uint32_t n = 0, m = 0;

@@ -43,8 +43,9 @@ struct RenderParams {
   // outputs
   double* out_rgb;                  // may be null (RTX_FLAG_NO_RADIANCE)
   uint32_t* out_ids;                // may be null
-  // Sample queue (rtx_render_pool.cu, SAMPLE_QUEUE): when tail_granules != 0 (then tail_first == 0 and
-  // tail_granules == all granules of the shard) the work queue hands out (granule, sample) pairs — one sample
+  uint32_t out_is_host;             // out_rgb is pinned host memory written over PCIe (queue plan, rtx_render_pool.cu)
+  // Sample queue (rtx_render_pool.cu, pool_plan_tail): when tail_granules != 0 (then tail_first == 0 and
+  // tail_granules == all granules of the shard) the work queue hands out (granule, sample) pairs — one camera path
   // per context — and per-sample radiance goes to tail_scratch[((g * rpp + s) * 32 + k) * 3 ..], which
   // tail_sum_kernel adds up per pixel in sample order (the reference's left fold).
   uint32_t tail_first, tail_granules;
@@ -78,8 +79,13 @@ __device__ __forceinline__ Granule decode_granule(const RenderParams& p, uint32_
 // pixel k (row-major inside the granule) → image pixel index and output index
 __device__ __forceinline__ void granule_pixel(const RenderParams& p, const Granule& g, uint32_t k, uint32_t* x, uint32_t* y,
                                               uint32_t* out_index) {
-  *x = g.x0 + k % g.w;
-  *y = g.y0 + k / g.w;
+  if (g.w == GRAN_W) {  // (warp-uniform) a full-width granule: no division
+    *x = g.x0 + (k & (GRAN_W - 1u));
+    *y = g.y0 + k / GRAN_W;
+  } else {
+    *x = g.x0 + k % g.w;
+    *y = g.y0 + k / g.w;
+  }
   *out_index = p.compact ? g.base_out + (*y - g.ty0) * TILE + (*x - g.tx0) : *y * p.width + *x;
 }
 

@@ -27,29 +27,31 @@
 
 namespace rtx {
 
-constexpr int POOL_WARPS = 8;    // warps per CTA
-constexpr int POOL_BLOCK = POOL_WARPS * 32;
+constexpr int POOL_WARPS_PIXEL_QUEUE = 20;  // resident warps per SM of the pixel-queue variant (pool_plan_tail)
 constexpr int POOL_SLOTS_MAX = 64;  // pixel contexts per warp (one bit each in a 64-bit state mask)
+constexpr int POOL_WARP_SCRATCH = POOL_SLOTS_MAX;  // per warp: compaction indices
 constexpr uint32_t FULLMASK = 0xFFFFFFFFu;
 constexpr uint32_t NO_PIXEL = 0xFFFFFFFFu;
 
-// Context fields, SoA per warp: word(f, slot) = pool[f * POOL_SLOTS + slot], 8 bytes each.
-enum : int {
-  F_POS = 0,     // 3  ray.position            (ray.rs:5)
-  F_DIR = 3,     // 3  ray.direction           (ray.rs:6)
-  F_LIGHT = 6,   // 3  ray.light_color         (ray.rs:8)
-  F_RES = 9,     // 3  ray.resulting_color     (ray.rs:7)
-  F_ACC = 12,    // 3  running sum of the pixel's samples (scene.rs:253-259)
-  F_FOCAL = 15,  // 3  camera.position + pixel_dir * focal_length (scene.rs:203), per pixel
-  F_RNG = 18,    // 1  WyRand state of the current (pixel, sample) stream
-  F_M0 = 19,     // 1  sample index | segment << 32
-  F_M1 = 20,     // 1  out_index | hit ref << 32
-  F_M2 = 21,     // 1  pixel index (NO_PIXEL = none) | hit object id << 32
-  F_M3 = 22,     // 1  SAMPLE_QUEUE: tail_scratch slot of this context's (pixel, sample)
-  F_COUNT = 23
-};
-template <int POOL_SLOTS>
+// Context fields, SoA per warp: word(f, slot) = pool[f * POOL_SLOTS + slot], 8 bytes each.  A pixel-queue
+// context keeps its pixel for all rpp samples (running sum + the pixel's focal point: 22 words); a sample-queue
+// context lives for one camera path (17 words).  Fewer words = more resident warps per SM.
+template <int POOL_SLOTS, bool SAMPLE_QUEUE>
 struct Pool {
+  enum : int {
+    F_POS = 0,     // 3  ray.position            (ray.rs:5)
+    F_DIR = 3,     // 3  ray.direction           (ray.rs:6)
+    F_LIGHT = 6,   // 3  ray.light_color         (ray.rs:8)
+    F_RES = 9,     // 3  ray.resulting_color     (ray.rs:7)
+    F_RNG = 12,    // 1  WyRand state of the current (pixel, sample) stream
+    F_M0 = 13,     // 1  sample index | segment << 32
+    F_M1 = 14,     // 1  out_index | hit ref << 32
+    F_M2 = 15,     // 1  pixel index (NO_PIXEL = none) | hit object id << 32
+    F_M3 = 16,     // 1  SAMPLE_QUEUE only: tail_scratch slot of this context's (pixel, sample)
+    F_ACC = 16,    // 3  pixel queue only: running sum of the pixel's samples (scene.rs:253-259)
+    F_FOCAL = 19,  // 3  pixel queue only: camera.position + pixel_dir * focal_length (scene.rs:203), per pixel
+    F_COUNT = SAMPLE_QUEUE ? 17 : 22
+  };
   static constexpr size_t BYTES_PER_WARP = (size_t)F_COUNT * POOL_SLOTS * 8;
   unsigned long long* w;  // this warp's fields
   __device__ __forceinline__ double ld(int f, uint32_t s) const { return __longlong_as_double((long long)w[f * POOL_SLOTS + s]); }
@@ -89,9 +91,13 @@ __global__ void __launch_bounds__(256) tail_sum_kernel(const __grid_constant__ R
   p.out_rgb[(size_t)out_index * 3 + 2] = px.z;
 }
 
-template <int POOL_SLOTS, int MIN_BLOCKS, bool SAMPLE_QUEUE>
-__global__ void __launch_bounds__(POOL_BLOCK, MIN_BLOCKS) render_pool_kernel(const __grid_constant__ RenderParams p) {
-  constexpr size_t POOL_BYTES_PER_WARP = Pool<POOL_SLOTS>::BYTES_PER_WARP;
+// Registers per thread that still let `warps` warps share an SM's 64 K registers (allocated 8 per thread at a time).
+constexpr int pool_max_regs(int warps) { return (65536 / (warps * 32)) / 8 * 8 > 128 ? 128 : (65536 / (warps * 32)) / 8 * 8; }
+
+template <int POOL_SLOTS, int MIN_BLOCKS, bool SAMPLE_QUEUE, int POOL_WARPS = 8>
+__global__ void __launch_bounds__(POOL_WARPS * 32, MIN_BLOCKS) __maxnreg__(pool_max_regs(POOL_WARPS * MIN_BLOCKS)) render_pool_kernel(const __grid_constant__ RenderParams p) {
+  constexpr int POOL_BLOCK = POOL_WARPS * 32;
+  constexpr size_t POOL_BYTES_PER_WARP = Pool<POOL_SLOTS, SAMPLE_QUEUE>::BYTES_PER_WARP;
   extern __shared__ __align__(128) unsigned char smem_raw[];
   // [0,128) mbarrier | scene blob | (128-aligned) POOL_WARPS pools | POOL_WARPS x 64-byte index scratch |
   // glibc sin/cos table (3520 B)
@@ -103,10 +109,14 @@ __global__ void __launch_bounds__(POOL_BLOCK, MIN_BLOCKS) render_pool_kernel(con
 
   const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
   const uint32_t lt_mask = (1u << lane) - 1u;
-  Pool<POOL_SLOTS> P;
+  using PoolT = Pool<POOL_SLOTS, SAMPLE_QUEUE>;
+  constexpr int F_POS = PoolT::F_POS, F_DIR = PoolT::F_DIR, F_LIGHT = PoolT::F_LIGHT, F_RES = PoolT::F_RES,
+                F_RNG = PoolT::F_RNG, F_M0 = PoolT::F_M0, F_M1 = PoolT::F_M1, F_M2 = PoolT::F_M2, F_M3 = PoolT::F_M3,
+                F_ACC = PoolT::F_ACC, F_FOCAL = PoolT::F_FOCAL;
+  PoolT P;
   P.w = reinterpret_cast<unsigned long long*>(smem_raw + pools_off + warp * POOL_BYTES_PER_WARP);
-  unsigned char* idx = smem_raw + pools_off + POOL_WARPS * POOL_BYTES_PER_WARP + warp * POOL_SLOTS_MAX;
-  double* sctab = reinterpret_cast<double*>(smem_raw + pools_off + POOL_WARPS * POOL_BYTES_PER_WARP + POOL_WARPS * POOL_SLOTS_MAX);
+  unsigned char* idx = smem_raw + pools_off + POOL_WARPS * POOL_BYTES_PER_WARP + warp * POOL_WARP_SCRATCH;
+  double* sctab = reinterpret_cast<double*>(smem_raw + pools_off + POOL_WARPS * POOL_BYTES_PER_WARP + POOL_WARPS * POOL_WARP_SCRATCH);
   for (uint32_t i = threadIdx.x; i < 440u; i += POOL_BLOCK) sctab[i] = SINCOS_TAB_DEV[i];
   __syncthreads();
 
@@ -129,7 +139,6 @@ __global__ void __launch_bounds__(POOL_BLOCK, MIN_BLOCKS) render_pool_kernel(con
   Granule g;
   g.x0 = g.y0 = g.w = g.npix = g.base_out = g.tx0 = g.ty0 = 0;
   uint32_t g_next = 0, g_sample = 0, g_slot_base = 0;
-  bool g_single = false;
   bool exhausted = false;
   uint32_t n_rays = 0, n_paths = 0, n_panics = 0, n_hits = 0;
 
@@ -206,7 +215,7 @@ __global__ void __launch_bounds__(POOL_BLOCK, MIN_BLOCKS) render_pool_kernel(con
           if (SAMPLE_QUEUE) {
             // single-sample context: this sample's radiance goes to the scratch, the context is free again
             double* dst = p.tail_scratch + (size_t)(uint32_t)P.ldu(F_M3, slot) * 3;
-            dst[0] = res.x, dst[1] = res.y, dst[2] = res.z;
+            dst[0] = res.x, dst[1] = res.y, dst[2] = res.z;  // (plain stores: __stcg's STG.STRONG.GPU cost 11 % of the kernel)
             P.stu(F_M2, slot, pack2(NO_PIXEL, 0));
             P.stu(F_M0, slot, 0);
           } else {
@@ -243,7 +252,7 @@ __global__ void __launch_bounds__(POOL_BLOCK, MIN_BLOCKS) render_pool_kernel(con
         pix = (uint32_t)P.ldu(F_M2, slot);
         sample = (uint32_t)P.ldu(F_M0, slot);
         out_index = (uint32_t)P.ldu(F_M1, slot);
-        if (pix != NO_PIXEL && sample == rpp) {
+        if (!SAMPLE_QUEUE && pix != NO_PIXEL && sample == rpp) {
           if (p.out_rgb) {
             const V3 px = P.ld3(F_ACC, slot) / (double)rpp;  // avg: `/ length` (scene.rs:258)
             p.out_rgb[(size_t)out_index * 3 + 0] = px.x;
@@ -253,6 +262,7 @@ __global__ void __launch_bounds__(POOL_BLOCK, MIN_BLOCKS) render_pool_kernel(con
           pix = NO_PIXEL;
         }
       }
+      V3 focal = mk3(0.0, 0.0, 0.0);  // SAMPLE_QUEUE: a context's focal point lives only inside this trip
       bool need = has && pix == NO_PIXEL;
       uint32_t need_m = __ballot_sync(FULLMASK, need);
       while (need_m != 0u && !exhausted) {
@@ -265,12 +275,11 @@ __global__ void __launch_bounds__(POOL_BLOCK, MIN_BLOCKS) render_pool_kernel(con
             break;
           }
           uint32_t gidx = w;
-          g_single = false, g_sample = 0, g_slot_base = 0;
+          g_sample = 0, g_slot_base = 0;
           if (SAMPLE_QUEUE) {  // a (granule, sample) entry: one sample per context
-            const uint32_t v = w - p.tail_first, tg = v / rpp;
-            g_sample = v - tg * rpp;
-            gidx = p.tail_first + tg;
-            g_single = true;
+            const uint32_t tg = w / rpp;
+            g_sample = w - tg * rpp;
+            gidx = tg;
             g_slot_base = (tg * rpp + g_sample) * GRAN_PIXELS;
           }
           g = decode_granule(p, gidx);
@@ -283,7 +292,6 @@ __global__ void __launch_bounds__(POOL_BLOCK, MIN_BLOCKS) render_pool_kernel(con
           granule_pixel(p, g, k, &x, &y, &out_index);
           pix = y * p.width + x;
           sample = g_sample;
-          if (SAMPLE_QUEUE) P.stu(F_M3, slot, pack2(g_slot_base + k, 0u));
           // scene.rs:213-222 with the libm calls hoisted to the host tables; camera.rs:65-67; scene.rs:203
           M3 to_world;
           to_world.x = mk3(p.to_world[0], p.to_world[1], p.to_world[2]);
@@ -291,8 +299,12 @@ __global__ void __launch_bounds__(POOL_BLOCK, MIN_BLOCKS) render_pool_kernel(con
           to_world.z = mk3(p.to_world[6], p.to_world[7], p.to_world[8]);
           const V3 cam_dir = mk3(p.sin_x[x], p.sin_y[y], fmul(p.cos_x[x], p.cos_y[y]));
           const V3 pix_dir = matvec(to_world, cam_dir);
-          P.st3(F_FOCAL, slot, cam_pos + pix_dir * p.focal_length);
-          P.st3(F_ACC, slot, mk3(0.0, 0.0, 0.0));  // iter_ops.rs:4-8: the fold starts from zeros()
+          focal = cam_pos + pix_dir * p.focal_length;
+          if (!SAMPLE_QUEUE) P.st3(F_FOCAL, slot, focal);
+          if (SAMPLE_QUEUE)
+            P.stu(F_M3, slot, pack2(g_slot_base + k, 0u));
+          else
+            P.st3(F_ACC, slot, mk3(0.0, 0.0, 0.0));  // iter_ops.rs:4-8: the fold starts from zeros()
           if (p.out_ids && g_sample == 0) p.out_ids[out_index] = MISS_ID;
           need = false;
           if (rpp == 0) {  // avg of an empty iterator: zeros / 0.0 = NaN (scene.rs:253-259)
@@ -316,7 +328,8 @@ __global__ void __launch_bounds__(POOL_BLOCK, MIN_BLOCKS) render_pool_kernel(con
         const double u0 = wy_f64(rng), u1 = wy_f64(rng), u2 = wy_f64(rng);
         const V3 pos = cam_pos + mk3(u0, u1, u2) * p.non_focal_offset;
         const double u3 = wy_f64(rng), u4 = wy_f64(rng), u5 = wy_f64(rng);
-        const V3 target = P.ld3(F_FOCAL, slot) + mk3(u3, u4, u5) * p.focal_offset;
+        // sample queue: every context that starts a path here was handed its pixel in this trip
+        const V3 target = (SAMPLE_QUEUE ? focal : P.ld3(F_FOCAL, slot)) + mk3(u3, u4, u5) * p.focal_offset;
         P.st3(F_POS, slot, pos);
         P.st3(F_DIR, slot, vnorm(target - pos));
         P.st3(F_LIGHT, slot, mk3(1.0, 1.0, 1.0));
@@ -359,29 +372,38 @@ bool pool_kernel_eligible(const RenderParams& p) {
          p.max_bounces < 0x7FFFFFFEull;
 }
 
-// Which queue this launch uses.  With whole-pixel entries a context runs its pixel's rpp samples one after
-// the other, so the kernel cannot end before the most expensive pixel handed out last has finished:
-// rpp x (up to max_bounces + 1) segments of latency — on S1 at 64 spp more than a millisecond of under-filled
-// machine per launch whatever the shard size, which is what limits strong scaling.  The SAMPLE_QUEUE hands
-// out (granule, sample) entries instead: the tail is one path, at the price of 24 B of scratch per path and
-// the ordered sum afterwards.  Chosen when rpp >= 4 and the scratch fits the budget
-// (RTX_FLAG_PIXEL_QUEUE / RTX_FLAG_SAMPLE_QUEUE force one or the other).
-// Returns the scratch bytes needed (0 = whole-pixel queue): [granules * rpp * 32 * 3] f64.
+// Which queue this launch uses.
+//   pixel queue   an entry is a whole granule and a context keeps its pixel for all rpp samples (running sum in the
+//                 context, 22 words, 20 warps per SM); no scratch, and every finished pixel is stored at once — a frame
+//                 in pinned host memory streams out over PCIe while the launch is still rendering.  But a warp's 64
+//                 contexts drift onto pixels of unrelated granules at unrelated depths (25.7 of 32 lanes per
+//                 instruction), and the launch cannot end before the last pixel handed out has run its rpp samples
+//                 one after the other.
+//   sample queue  an entry is a (granule, sample): one camera path per context (17 words, 24 warps per SM), per-sample
+//                 radiance to a 24 B scratch slot, tail_sum_kernel adds up afterwards.  A warp works on one or two
+//                 granules at a time (28.1 lanes per instruction) and the launch ends within one path of the last
+//                 entry: C2 11.35 ms against 12.2 ms, a 1/8 shard 1.65 against 2.8 ms.  The frame only appears in
+//                 the sum pass, which is an exposed PCIe write when it goes straight to host memory (C2 e2e 14.1 ms).
+// Auto: the sample queue when rpp >= 4 and the scratch fits the budget — except for a large frame rendered straight
+// into pinned host memory, where the pixel queue's overlapped stores win (C2 e2e 12.3 ms).
+// RTX_FLAG_PIXEL_QUEUE / RTX_FLAG_SAMPLE_QUEUE force one.  The image is the same either way.
+// Returns the scratch bytes needed (0 = pixel queue): [granules * rpp * 32 * 3] f64.
 size_t pool_plan_tail(RenderParams& p, int sm_count) {
   const uint64_t granules = (uint64_t)p.my_tiles * GRANS_PER_TILE;
   p.tail_first = (uint32_t)granules;
   p.tail_granules = 0;
   p.tail_scratch = nullptr;
   p.tail_done = nullptr;
-  const int force = p.queue_mode == 1 ? 0 : (p.queue_mode == 2 ? 1 : -1);
+  // RTX_QUEUE_MODE (measurement knob, only when the caller left the choice open): 1 pixel queue, 2 sample queue
+  static const int env_mode = [] { const char* v = getenv("RTX_QUEUE_MODE"); return v ? atoi(v) : 0; }();
+  const uint32_t mode = p.queue_mode ? p.queue_mode : (uint32_t)env_mode;
   const uint64_t rpp = p.rays_per_pixel;
-  if (force == 0 || !p.out_rgb || rpp < 1 || rpp > 65536) return 0;
-  if (force != 1 && rpp < 4) return 0;
-  // Whole-pixel entries are ~4 % faster in the steady state (no scratch, no sum pass): keep them when every
-  // resident context gets many pixels, so the tail is a small share (measured cross-over: N = 1 at 1080p,
-  // 13.7 pixels per context, 12.32 vs 12.77 ms; N = 2, 6.8 per context, 6.72 vs 6.41 ms).
-  const uint64_t contexts = (uint64_t)sm_count * 2 * POOL_WARPS * POOL_SLOTS_MAX;
-  if (force != 1 && granules * GRAN_PIXELS >= 10 * contexts) return 0;
+  if (mode == 1 || !p.out_rgb || rpp < 1 || rpp > 65536) return 0;
+  if (mode != 2 && rpp < 4) return 0;
+  // a frame is "large" when every resident context gets many pixels, so that draining is a small share of the launch
+  const uint64_t contexts = (uint64_t)sm_count * POOL_WARPS_PIXEL_QUEUE * POOL_SLOTS_MAX;
+  const bool large = granules * GRAN_PIXELS >= 10 * contexts;
+  if (mode != 2 && large && p.out_is_host) return 0;
   const uint64_t cap_bytes = 4ull << 30;  // scratch budget
   const uint64_t bytes = granules * rpp * GRAN_PIXELS * 24;
   if (bytes > cap_bytes || granules * rpp * GRAN_PIXELS > 0xFFFFFFFFull) return 0;
@@ -390,10 +412,17 @@ size_t pool_plan_tail(RenderParams& p, int sm_count) {
   return (size_t)bytes;
 }
 
-template <int POOL_SLOTS, int MIN_BLOCKS, bool SAMPLE_QUEUE>
+// Dynamic shared memory of one CTA of a variant: mbarrier | blob | pools | index scratch | sin/cos table.
+template <int POOL_SLOTS, bool SAMPLE_QUEUE, int POOL_WARPS>
+static size_t pool_smem_bytes(uint32_t blob_bytes) {
+  const size_t pools_off = (128u + (size_t)blob_bytes + 127u) & ~(size_t)127u;
+  return pools_off + POOL_WARPS * Pool<POOL_SLOTS, SAMPLE_QUEUE>::BYTES_PER_WARP + POOL_WARPS * POOL_WARP_SCRATCH + 440 * sizeof(double);
+}
+
+template <int POOL_SLOTS, int MIN_BLOCKS, bool SAMPLE_QUEUE, int POOL_WARPS = 8>
 static cudaError_t launch_pool_variant(const RenderParams& p, int sm_count, cudaStream_t stream, uint32_t* out_launches) {
-  const size_t pools_off = (128u + (size_t)p.layout.bytes + 127u) & ~(size_t)127u;
-  const size_t smem = pools_off + POOL_WARPS * Pool<POOL_SLOTS>::BYTES_PER_WARP + POOL_WARPS * POOL_SLOTS_MAX + 440 * sizeof(double);
+  constexpr int POOL_BLOCK = POOL_WARPS * 32;
+  const size_t smem = pool_smem_bytes<POOL_SLOTS, SAMPLE_QUEUE, POOL_WARPS>(p.layout.bytes);
   cudaError_t e = cudaMemsetAsync(p.work_counter, 0, sizeof(uint32_t), stream);
   if (e != cudaSuccess) return e;
   const uint64_t total_work = (uint64_t)p.tail_first + (uint64_t)p.tail_granules * p.rays_per_pixel;
@@ -402,24 +431,46 @@ static cudaError_t launch_pool_variant(const RenderParams& p, int sm_count, cuda
   uint64_t want_blocks = (total_work + per_block - 1) / per_block;
   uint64_t grid = (uint64_t)sm_count * MIN_BLOCKS;
   if (want_blocks < grid) grid = want_blocks ? want_blocks : 1;
-  e = cudaFuncSetAttribute(render_pool_kernel<POOL_SLOTS, MIN_BLOCKS, SAMPLE_QUEUE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  e = cudaFuncSetAttribute(render_pool_kernel<POOL_SLOTS, MIN_BLOCKS, SAMPLE_QUEUE, POOL_WARPS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return e;
-  render_pool_kernel<POOL_SLOTS, MIN_BLOCKS, SAMPLE_QUEUE><<<(unsigned)grid, POOL_BLOCK, smem, stream>>>(p);
+  render_pool_kernel<POOL_SLOTS, MIN_BLOCKS, SAMPLE_QUEUE, POOL_WARPS><<<(unsigned)grid, POOL_BLOCK, smem, stream>>>(p);
   if (out_launches) *out_launches += 1;
   e = cudaGetLastError();
-  if (e != cudaSuccess || !SAMPLE_QUEUE) return e;
+  if (e != cudaSuccess || p.tail_granules == 0) return e;
   const unsigned threads = p.tail_granules * GRAN_PIXELS;
   tail_sum_kernel<<<(threads + 255) / 256, 256, 0, stream>>>(p);
   if (out_launches) *out_launches += 1;
   return cudaGetLastError();
 }
 
+// Largest dynamic shared memory one CTA may ask for on the current device (227 KB on sm_100).
+static size_t pool_smem_optin() {
+  int dev = 0, v = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || cudaDeviceGetAttribute(&v, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev) != cudaSuccess)
+    return 0;
+  return (size_t)v;
+}
+
+// Variants.  The kernel is issue/latency bound (ncu: 62 % of issue slots used with 4 warps per scheduler), so
+// the wide variants put ONE CTA of 20 (pixel queue: 22-word contexts, 92 registers) or 24 (sample queue: 17-word
+// contexts, 80 registers) warps on an SM, all with 64 contexts per warp; they need almost all of the SM's shared
+// memory, so scenes whose blob does not fit next to the pools use the 2 x 8-warp variant.  Measured on C2
+// (profiles/r01_SUMMARY.md): 2 x 8 warps 13.00 ms, 1 x 20 warps 12.20 ms.
 cudaError_t launch_render_pool(const RenderParams& p, int sm_count, cudaStream_t stream, uint32_t* out_launches) {
-  // RTX_POOL_VARIANT (measurement knob): 0 = 64 contexts/warp, 2 CTAs/SM; 1 = 48 contexts/warp, 3 CTAs/SM
+  // RTX_POOL_VARIANT (measurement knob): 0 = auto; 1 = 2 CTAs x 8 warps; 2 = 1 x 20 warps; 3 = 1 x 24 warps (sample queue only)
   static const int variant = [] { const char* v = getenv("RTX_POOL_VARIANT"); return v ? atoi(v) : 0; }();
-  if (p.tail_granules != 0) return launch_pool_variant<64, 2, true>(p, sm_count, stream, out_launches);
-  if (variant == 1) return launch_pool_variant<48, 3, false>(p, sm_count, stream, out_launches);
-  return launch_pool_variant<64, 2, false>(p, sm_count, stream, out_launches);
+  static const size_t optin = pool_smem_optin();
+  const uint32_t blob = p.layout.bytes;
+  if (p.tail_granules != 0) {  // sample queue
+    if ((variant == 0 || variant == 3) && pool_smem_bytes<64, true, 24>(blob) <= optin)
+      return launch_pool_variant<64, 1, true, 24>(p, sm_count, stream, out_launches);
+    if ((variant == 0 || variant == 2) && pool_smem_bytes<64, true, 20>(blob) <= optin)
+      return launch_pool_variant<64, 1, true, 20>(p, sm_count, stream, out_launches);
+    return launch_pool_variant<64, 2, true, 8>(p, sm_count, stream, out_launches);
+  }
+  if ((variant == 0 || variant == 2) && pool_smem_bytes<64, false, 20>(blob) <= optin)
+    return launch_pool_variant<64, 1, false, 20>(p, sm_count, stream, out_launches);
+  return launch_pool_variant<64, 2, false, 8>(p, sm_count, stream, out_launches);
 }
 
 }  // namespace rtx

@@ -453,6 +453,11 @@ class Scene:
                                                        C.byref(sh) if sh is not None else None,
                                                        d_rgb, d_ids, d_counters, stream), h)
 
+    @property
+    def last_device_launches(self):
+        """Kernels launched by the most recent render_device call."""
+        return int(_abi.load().rtx_scene_last_launches(self._handle)) if self._handle is not None else 0
+
     # -- per-function device evaluation (parity tests) ---------------------------------------------
     def debug_closest_object(self, rays, flags=RTX_ACCEL_BRUTE):
         h = self._sync()

@@ -106,6 +106,7 @@ SIGNATURES = {
     "rtx_scene_rebuild_accel": (C.c_int32, [_vp]),
     "rtx_scene_accel_refits": (C.c_uint32, [_vp]),
     "rtx_scene_accel_builds": (C.c_uint32, [_vp]),
+    "rtx_scene_last_launches": (C.c_uint32, [_vp]),
     "rtx_scene_object_count": (C.c_uint64, [_vp]),
     "rtx_scene_render": (C.c_int32, [_vp, C.c_uint32, C.c_uint32, C.c_uint64, C.c_uint32, _vp, _vp, _P(Stats)]),
     "rtx_scene_render_device": (C.c_int32, [_vp, C.c_uint32, C.c_uint32, C.c_uint64, C.c_uint32, _P(Shard),

@@ -69,6 +69,7 @@ extern "C" {
     pub fn rtx_scene_rebuild_accel(scene: *mut rtx_scene) -> rtx_status;
     pub fn rtx_scene_accel_refits(scene: *const rtx_scene) -> u32;
     pub fn rtx_scene_accel_builds(scene: *const rtx_scene) -> u32;
+    pub fn rtx_scene_last_launches(scene: *const rtx_scene) -> u32;
     pub fn rtx_peer_alloc(device: i32, bytes: u64, out_d_ptr: *mut *mut c_void) -> rtx_status;
     pub fn rtx_peer_free(device: i32, d_ptr: *mut c_void) -> rtx_status;
     pub fn rtx_peer_export(device: i32, d_ptr: *mut c_void, out_handle: *mut u8) -> rtx_status;

@@ -277,3 +277,11 @@ def test_c2_full_size_frame_equals_oracle(rtx, oracle, gpu):
     assert sc.last_stats.rays == ref["rays"] == 245087388
     assert float(np.abs(rgb - ref["rgb"]).max()) <= 1e-4 and psnr(rgb, ref["rgb"]) >= PSNR_MIN  # the north-star gates
     assert rgb.tobytes() == ref["rgb"].tobytes()  # the bar this repo holds: bit-exact
+    # the same frame under the pixel queue: a pinned caller buffer (auto: pixels stored over PCIe by the kernel)
+    # and forced on a device frame
+    import torch
+    pin = torch.full((1080, 1920, 3), -1.0, dtype=torch.float64).pin_memory()
+    b = sc.render(1920, 1080, seed=1, out=pin.numpy())
+    assert b.tobytes() == ref["rgb"].tobytes()
+    c = sc.render(1920, 1080, seed=1, flags=rtx.RTX_FLAG_PIXEL_QUEUE)
+    assert c.tobytes() == ref["rgb"].tobytes()
