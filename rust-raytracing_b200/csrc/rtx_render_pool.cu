@@ -32,6 +32,8 @@ constexpr int POOL_SLOTS_MAX = 64;  // pixel contexts per warp (one bit each in 
 constexpr int POOL_WARP_SCRATCH = POOL_SLOTS_MAX;  // per warp: compaction indices
 constexpr uint32_t FULLMASK = 0xFFFFFFFFu;
 constexpr uint32_t NO_PIXEL = 0xFFFFFFFFu;
+// Sample queue: consecutive samples of a granule one queue entry covers (one atomic + one granule decode per entry)
+constexpr uint32_t SAMPLES_PER_ENTRY = 4;
 
 // Context fields, SoA per warp: word(f, slot) = pool[f * POOL_SLOTS + slot], 8 bytes each.  A pixel-queue
 // context keeps its pixel for all rpp samples (running sum + the pixel's focal point: 22 words); a sample-queue
@@ -123,7 +125,8 @@ __global__ void __launch_bounds__(POOL_WARPS * 32, MIN_BLOCKS) __maxnreg__(pool_
   const V3 cam_pos = mk3(p.cam_pos[0], p.cam_pos[1], p.cam_pos[2]);
   const uint32_t rpp = (uint32_t)p.rays_per_pixel;
   const uint32_t max_segments = (uint32_t)p.max_bounces + 1u;  // scene.rs:227
-  const uint32_t total_work = p.tail_first + p.tail_granules * rpp;
+  const uint32_t entries_per_granule = (rpp + SAMPLES_PER_ENTRY - 1u) / SAMPLES_PER_ENTRY;
+  const uint32_t total_work = p.tail_first + p.tail_granules * entries_per_granule;
 
   // every context starts without a pixel, in REGEN
   P.stu(F_M2, lane, pack2(NO_PIXEL, 0));
@@ -138,7 +141,7 @@ __global__ void __launch_bounds__(POOL_WARPS * 32, MIN_BLOCKS) __maxnreg__(pool_
   // warp-uniform work-queue state (granule = 8x4 pixels of a 16x16 tile, as in render_megakernel)
   Granule g;
   g.x0 = g.y0 = g.w = g.npix = g.base_out = g.tx0 = g.ty0 = 0;
-  uint32_t g_next = 0, g_sample = 0, g_slot_base = 0;
+  uint32_t g_next = 0, g_sample = 0, g_sample_end = 0, g_slot_base = 0;
   bool exhausted = false;
   uint32_t n_rays = 0, n_paths = 0, n_panics = 0, n_hits = 0;
 
@@ -267,6 +270,12 @@ __global__ void __launch_bounds__(POOL_WARPS * 32, MIN_BLOCKS) __maxnreg__(pool_
       uint32_t need_m = __ballot_sync(FULLMASK, need);
       while (need_m != 0u && !exhausted) {
         if (g_next >= g.npix) {
+          if (SAMPLE_QUEUE && g_sample + 1u < g_sample_end) {  // next sample of the entry
+            ++g_sample;
+            g_slot_base += GRAN_PIXELS;
+            g_next = 0;
+            continue;
+          }
           uint32_t w = 0;
           if (lane == 0) w = atomicAdd(p.work_counter, 1u);
           w = __shfl_sync(FULLMASK, w, 0);
@@ -276,9 +285,10 @@ __global__ void __launch_bounds__(POOL_WARPS * 32, MIN_BLOCKS) __maxnreg__(pool_
           }
           uint32_t gidx = w;
           g_sample = 0, g_slot_base = 0;
-          if (SAMPLE_QUEUE) {  // a (granule, sample) entry: one sample per context
-            const uint32_t tg = w / rpp;
-            g_sample = w - tg * rpp;
+          if (SAMPLE_QUEUE) {  // a (granule, samples [g_sample, g_sample_end)) entry: one sample per context
+            const uint32_t tg = w / entries_per_granule;
+            g_sample = (w - tg * entries_per_granule) * SAMPLES_PER_ENTRY;
+            g_sample_end = min(rpp, g_sample + SAMPLES_PER_ENTRY);
             gidx = tg;
             g_slot_base = (tg * rpp + g_sample) * GRAN_PIXELS;
           }
@@ -425,9 +435,12 @@ static cudaError_t launch_pool_variant(const RenderParams& p, int sm_count, cuda
   const size_t smem = pool_smem_bytes<POOL_SLOTS, SAMPLE_QUEUE, POOL_WARPS>(p.layout.bytes);
   cudaError_t e = cudaMemsetAsync(p.work_counter, 0, sizeof(uint32_t), stream);
   if (e != cudaSuccess) return e;
-  const uint64_t total_work = (uint64_t)p.tail_first + (uint64_t)p.tail_granules * p.rays_per_pixel;
+  const uint64_t total_work =
+      (uint64_t)p.tail_first + (uint64_t)p.tail_granules * ((p.rays_per_pixel + SAMPLES_PER_ENTRY - 1) / SAMPLES_PER_ENTRY);
   // persistent grid: MIN_BLOCKS CTAs per SM, never more contexts than queue entries can feed
-  const uint64_t per_block = (uint64_t)POOL_WARPS * POOL_SLOTS / GRAN_PIXELS;  // queue entries one CTA can hold at once
+  // queue entries one CTA can hold at once (a sample-queue entry is up to SAMPLES_PER_ENTRY x 32 camera paths)
+  const uint64_t entry_paths = GRAN_PIXELS * (SAMPLE_QUEUE ? (p.rays_per_pixel < SAMPLES_PER_ENTRY ? p.rays_per_pixel : SAMPLES_PER_ENTRY) : 1);
+  const uint64_t per_block = ((uint64_t)POOL_WARPS * POOL_SLOTS + entry_paths - 1) / entry_paths;
   uint64_t want_blocks = (total_work + per_block - 1) / per_block;
   uint64_t grid = (uint64_t)sm_count * MIN_BLOCKS;
   if (want_blocks < grid) grid = want_blocks ? want_blocks : 1;
