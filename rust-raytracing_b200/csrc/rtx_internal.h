@@ -77,6 +77,10 @@ struct rtx_scene {
 
   cudaStream_t stream = nullptr;  // used by the blocking host-buffer entry points
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+  // banded host output (rtx_scene_render into pinned memory): a copy stream and one event per band + one for the end
+  cudaStream_t copy_stream = nullptr;
+  static constexpr uint32_t MAX_BANDS = 8;
+  cudaEvent_t ev_band[MAX_BANDS + 1] = {};
 };
 
 namespace rtx {
@@ -91,6 +95,9 @@ cudaError_t launch_render(const RenderParams& p, int sm_count, cudaStream_t stre
 bool pool_kernel_eligible(const RenderParams& p);
 // Fills p.tail_first / p.tail_granules; returns the bytes p.tail_scratch must hold (0 = no tail region).
 size_t pool_plan_tail(RenderParams& p, int sm_count);
+// Bands (1..8) a large frame bound for pinned host memory is rendered in, sample queue each, so that a band's
+// device-to-host copy overlaps the next band's render; 1 = not worth it / not possible.
+uint32_t pool_host_bands(const RenderParams& p, int sm_count);
 cudaError_t launch_render_pool(const RenderParams& p, int sm_count, cudaStream_t stream, uint32_t* out_launches);
 // Builds the LBVH trees if the object list changed since the last build.  Synchronous.
 rtx_status ensure_lbvh(rtx_scene* s, cudaStream_t stream);

@@ -90,7 +90,7 @@ __global__ void __launch_bounds__(RENDER_BLOCK, USE_BVH ? BVH_BLOCKS_PER_SM : 2)
           exhausted = true;
           break;
         }
-        const uint32_t ltile = w / GRANS_PER_TILE, sub = w % GRANS_PER_TILE;
+        const uint32_t ltile = p.tile_first + w / GRANS_PER_TILE, sub = w % GRANS_PER_TILE;
         const uint32_t gtile = ltile * p.shard_count + p.shard_index;
         const uint32_t ty = gtile / p.tiles_x, tx = gtile % p.tiles_x;
         g_tx0 = tx * TILE;

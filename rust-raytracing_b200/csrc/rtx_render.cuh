@@ -37,7 +37,8 @@ struct RenderParams {
   // image shard
   uint32_t shard_index, shard_count;
   uint32_t tiles_x, tiles_y;
-  uint32_t my_tiles;    // tiles owned by this shard
+  uint32_t my_tiles;    // tiles of this shard this launch renders ...
+  uint32_t tile_first;  // ... starting at this one (a band of the shard's tile list; 0 = from the start)
   uint32_t compact;     // 1: outputs use the compact per-shard tile layout
   uint32_t* work_counter;  // zeroed before launch
   // outputs
@@ -62,7 +63,7 @@ struct Granule {
 // gidx = index of the granule within this shard's tile list (local tile = gidx / GRANS_PER_TILE).
 __device__ __forceinline__ Granule decode_granule(const RenderParams& p, uint32_t gidx) {
   Granule g;
-  const uint32_t ltile = gidx / GRANS_PER_TILE, sub = gidx % GRANS_PER_TILE;
+  const uint32_t ltile = p.tile_first + gidx / GRANS_PER_TILE, sub = gidx % GRANS_PER_TILE;
   const uint32_t gtile = ltile * p.shard_count + p.shard_index;
   const uint32_t ty = gtile / p.tiles_x, tx = gtile % p.tiles_x;
   g.tx0 = tx * TILE;

@@ -422,6 +422,22 @@ size_t pool_plan_tail(RenderParams& p, int sm_count) {
   return (size_t)bytes;
 }
 
+uint32_t pool_host_bands(const RenderParams& p, int sm_count) {
+  if (p.queue_mode != 0 || !p.out_rgb || p.shard_count != 1 || p.rays_per_pixel < 4 || p.rays_per_pixel > 65536) return 1;
+  static const int env_bands = [] { const char* v = getenv("RTX_HOST_BANDS"); return v ? atoi(v) : 0; }();  // measurement knob
+  const uint64_t contexts = (uint64_t)sm_count * 24 * POOL_SLOTS_MAX;
+  const uint64_t pixels = (uint64_t)p.width * p.height;
+  // measured on C2 (9.1 pixels per context): 1 band (pixel queue, zero-copy) 12.21 ms, 2: 11.57, 3: 11.46, 4: 11.39, 6: 11.42, 8: 11.43
+  uint32_t bands = pixels >= 8 * contexts ? 4u : (pixels >= 4 * contexts ? 2u : 1u);
+  if (env_bands > 0) bands = (uint32_t)env_bands;
+  if (bands > 8u) bands = 8u;
+  if (bands > p.tiles_y) bands = p.tiles_y;
+  // every band's scratch has to fit the budget of pool_plan_tail
+  const uint64_t band_pixels = ((uint64_t)(p.tiles_y + bands - 1) / bands) * p.tiles_x * TILE * TILE;
+  if (band_pixels * p.rays_per_pixel * 24 > (4ull << 30)) return 1;
+  return bands < 1u ? 1u : bands;
+}
+
 // Dynamic shared memory of one CTA of a variant: mbarrier | blob | pools | index scratch | sin/cos table.
 template <int POOL_SLOTS, bool SAMPLE_QUEUE, int POOL_WARPS>
 static size_t pool_smem_bytes(uint32_t blob_bytes) {
