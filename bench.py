@@ -307,8 +307,9 @@ def run_b200(args):
                    if args.gather == "p2p" else
                    "rtx_scene_render_device per rank + NCCL gather + rtx_deinterleave_tiles + D2H on rank 0"),
            "ms_per_step": float(te.item()) / K * 1e3, "frame_equals_device_frame": e2e_checked,
-           "d2h": "none: pinned caller buffer is written by the render kernel (posted PCIe stores, overlapped with "
-                  "rendering)" if world == 1 and os.environ.get("RTX_ZERO_COPY", "1") != "0" else "cudaMemcpyAsync"}
+           "d2h": ("inside rtx_scene_render: the frame is rendered in 4 bands of tile rows into a device frame; each band's "
+                   "cudaMemcpyAsync to the pinned caller buffer runs on a copy stream while the next band renders"
+                   if world == 1 else "cudaMemcpyAsync of rank 0's frame to pinned host memory after the step")}
 
     if world > 1 and args.gather == "p2p":
         frame.close()
