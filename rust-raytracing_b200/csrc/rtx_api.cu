@@ -336,7 +336,10 @@ static rtx_status render_common(rtx_scene* s, uint32_t width, uint32_t height, u
     p.out_rgb = s->d_rgb;
     p.out_is_host = 0;
     for (uint32_t b = 0; b < bands; ++b) {
-      const uint32_t r0 = (uint32_t)((uint64_t)p.tiles_y * b / bands), r1 = (uint32_t)((uint64_t)p.tiles_y * (b + 1) / bands);
+      // the last band is half as tall as the others: its copy is the one nothing overlaps
+      const uint64_t den = 2ull * bands - 1ull;
+      const uint32_t r0 = (uint32_t)((uint64_t)p.tiles_y * (2ull * b) / den);
+      const uint32_t r1 = b + 1 == bands ? p.tiles_y : (uint32_t)((uint64_t)p.tiles_y * (2ull * (b + 1)) / den);
       if (r1 == r0) continue;
       p.tile_first = r0 * p.tiles_x;
       p.my_tiles = (r1 - r0) * p.tiles_x;

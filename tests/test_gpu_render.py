@@ -304,3 +304,32 @@ def test_banded_host_output_equals_oracle(rtx, oracle, gpu, w, h):
     assert st[0] == ref["rays"] and st[1] == w * h * 4
     assert np.array_equal(ids, ref["ids"])
     assert rgb.tobytes() == ref["rgb"].tobytes()
+
+
+def test_queue_plan_selection_and_launch_count(rtx, gpu):
+    """rtx_scene_last_launches reports what the plan launched: the sample queue (render kernel + ordered-sum pass)
+    whenever rays_per_pixel >= 4, the pixel queue (one kernel) below that, when forced, and for ids-only renders;
+    LBVH scenes always one kernel."""
+    import torch
+    from rtx_b200 import scenes
+    dev = torch.device("cuda", 0)
+    w, h = 320, 200
+    rgb = torch.empty((h, w, 3), dtype=torch.float64, device=dev)
+    ids = torch.empty((h, w), dtype=torch.int32, device=dev)
+    st = torch.cuda.current_stream(dev).cuda_stream
+
+    def launches(sc, flags, want_rgb=True):
+        sc.render_device(w, h, 1, flags, None, rgb.data_ptr() if want_rgb else None, ids.data_ptr(), None, st)
+        torch.cuda.synchronize()
+        return sc.last_device_launches
+
+    s8 = scenes.sphere_demo(rays_per_pixel=8, max_bounces=4)
+    s2 = scenes.sphere_demo(rays_per_pixel=2, max_bounces=4)
+    assert launches(s8, rtx.RTX_ACCEL_AUTO) == 2
+    assert launches(s8, rtx.RTX_FLAG_PIXEL_QUEUE) == 1
+    assert launches(s8, rtx.RTX_FLAG_LANE_KERNEL) == 1
+    assert launches(s8, rtx.RTX_FLAG_NO_RADIANCE, want_rgb=False) == 1
+    assert launches(s2, rtx.RTX_ACCEL_AUTO) == 1
+    assert launches(s2, rtx.RTX_FLAG_SAMPLE_QUEUE) == 2
+    big = scenes.random_spheres(n=300, rays_per_pixel=8, max_bounces=2)
+    assert launches(big, rtx.RTX_ACCEL_LBVH) == 1
