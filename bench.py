@@ -277,6 +277,10 @@ def run_b200(args):
             scene._synced_batches = 0
             scene.render(W, H, seed=SEED, out=pin.numpy())
             return scene.last_stats.rays
+        if args.gather == "p2p":
+            # the frame goes to rank 0's pinned host memory band by band while the next band renders on every rank
+            frame.render_to_host(scene, SEED, pin, counters)
+            return None
         out = step(SEED)
         if rank == 0:
             pin.copy_(out, non_blocking=True)
@@ -291,7 +295,12 @@ def run_b200(args):
     sync_all()
     e2e_s = time.perf_counter() - t0
     # the frame the e2e call left in host memory is the frame the device-timed call left in HBM
-    e2e_checked = bool(torch.equal(pin, rgb.cpu())) if world == 1 else None
+    if world == 1:
+        e2e_checked = bool(torch.equal(pin, rgb.cpu()))
+    elif args.gather == "p2p" and rank == 0:
+        e2e_checked = bool(torch.equal(pin, frame_rgb.cpu()))
+    else:
+        e2e_checked = None
     if e2e_checked is False:
         raise SystemExit("e2e frame (host buffer) differs from the device-resident frame")
     te = torch.tensor([e2e_s], dtype=torch.float64, device=dev)
@@ -303,13 +312,16 @@ def run_b200(args):
     e2e = {"value": rays_per_step * K / float(te.item()) / 1e6, "unit": "Mrays/s",
            "h2d_bytes_per_step": int(blob_bytes), "d2h_bytes_per_step": int(npix * 24 + 32),
            "api": "rtx_scene_render (host buffers, pinned)" if world == 1 else
-                  ("rtx_scene_render_device per rank (RTX_FLAG_SHARD_IN_PLACE into rank 0's peer frame) + D2H on rank 0"
+                  ("rtx_scene_render_device_band per rank (RTX_FLAG_SHARD_IN_PLACE into rank 0's peer frame) + banded D2H on rank 0"
                    if args.gather == "p2p" else
                    "rtx_scene_render_device per rank + NCCL gather + rtx_deinterleave_tiles + D2H on rank 0"),
            "ms_per_step": float(te.item()) / K * 1e3, "frame_equals_device_frame": e2e_checked,
            "d2h": ("inside rtx_scene_render: the frame is rendered in 4 bands of tile rows into a device frame; each band's "
                    "cudaMemcpyAsync to the pinned caller buffer runs on a copy stream while the next band renders"
-                   if world == 1 else "cudaMemcpyAsync of rank 0's frame to pinned host memory after the step")}
+                   if world == 1 else
+                   ("PeerFrame.render_to_host: 4 bands; after a band's completion barrier rank 0's copy engine moves its rows to "
+                    "pinned host memory while every rank renders the next band" if args.gather == "p2p" else
+                    "cudaMemcpyAsync of rank 0's frame to pinned host memory after the step"))}
 
     if world > 1 and args.gather == "p2p":
         frame.close()

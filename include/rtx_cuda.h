@@ -172,6 +172,16 @@ rtx_status rtx_scene_render(rtx_scene* scene, uint32_t width, uint32_t height, u
 rtx_status rtx_scene_render_device(rtx_scene* scene, uint32_t width, uint32_t height, uint64_t seed, uint32_t flags,
                                    const rtx_shard* shard, void* d_out_rgb, void* d_out_primary_hit_id,
                                    void* d_out_counters, void* cuda_stream);
+/* The same for a BAND of the image only: the rows of RTX_TILE x RTX_TILE tiles [tile_row_first, tile_row_first +
+ * tile_row_count), i.e. pixel rows [16 first, min(height, 16 (first + count))), of the shard's tiles.  Buffers are
+ * those of the whole frame (or of the whole compact shard); pixels outside the band are not touched.  Rendering
+ * all bands of a frame gives the bytes of one rtx_scene_render_device call.  A caller pipelines with it: while
+ * band b+1 renders, band b — complete on every rank after a barrier — is already being copied out.
+ * (≙ the row-wise hand-over of Scene::render's join, raytracing/scene.rs:167-169)                          */
+rtx_status rtx_scene_render_device_band(rtx_scene* scene, uint32_t width, uint32_t height, uint64_t seed, uint32_t flags,
+                                        const rtx_shard* shard, uint32_t tile_row_first, uint32_t tile_row_count,
+                                        void* d_out_rgb, void* d_out_primary_hit_id, void* d_out_counters,
+                                        void* cuda_stream);
 /* Number of tiles (and therefore compact-buffer slots) shard `index` of `count` owns. */
 uint64_t   rtx_shard_tile_count(uint32_t width, uint32_t height, uint32_t index, uint32_t count);
 /* Scatter gathered compact shard buffers (rank-major: [count][slots][RTX_TILE][RTX_TILE][...]) into

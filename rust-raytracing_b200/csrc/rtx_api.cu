@@ -3,6 +3,7 @@
 // Host-side mirror of raytracing/scene.rs (Scene::new / add_object / render / render_to_image) and
 // raytracing/camera.rs (Camera::new / set_direction / to_*_space).  The hot path itself lives in
 // rtx_render.cu; nothing here computes a pixel on the CPU.
+#include <algorithm>
 #include <chrono>
 #include <cmath>
 #include <cstdlib>
@@ -269,7 +270,8 @@ static T* mapped_device_pointer(T* host) {
 static rtx_status render_common(rtx_scene* s, uint32_t width, uint32_t height, uint64_t seed, uint32_t flags,
                                 const rtx_shard* shard, double* d_rgb, uint32_t* d_ids,
                                 unsigned long long* d_counters, uint32_t* d_work_counter, cudaStream_t stream,
-                                uint32_t* launches, double* host_rgb = nullptr) {
+                                uint32_t* launches, double* host_rgb = nullptr, const uint32_t* tile_rows = nullptr) {
+  // tile_rows != null: {first, count} — only that band of tile rows (rtx_scene_render_device_band)
   // host_rgb != null: d_rgb is the device alias of that pinned caller buffer (rtx_scene_render)
   const bool rgb_is_host = host_rgb != nullptr;
   if (width == 0 || height == 0) return fail(s, RTX_ERR_INVALID_ARGUMENT, "width and height must be non-zero");
@@ -320,6 +322,15 @@ static rtx_status render_common(rtx_scene* s, uint32_t width, uint32_t height, u
   p.out_ids = d_ids;
   p.out_is_host = rgb_is_host ? 1u : 0u;
   p.ray_counter = d_counters;
+  if (tile_rows) {
+    // tile t of the image belongs to shard t mod count as its local tile t div count: a band of tile rows is a
+    // contiguous range of local tiles
+    const uint64_t lo = std::min<uint64_t>((uint64_t)tile_rows[0], p.tiles_y) * p.tiles_x;
+    const uint64_t hi = std::min<uint64_t>((uint64_t)tile_rows[0] + tile_rows[1], p.tiles_y) * p.tiles_x;
+    auto local_below = [&](uint64_t g) { return g > sh.index ? (g - sh.index + sh.count - 1) / sh.count : 0ull; };
+    p.tile_first = (uint32_t)local_below(lo);
+    p.my_tiles = (uint32_t)(local_below(hi) - local_below(lo));
+  }
   if (p.my_tiles == 0) return RTX_OK;
   p.tail_first = p.my_tiles * GRANS_PER_TILE, p.tail_granules = 0, p.tail_scratch = nullptr, p.tail_done = nullptr;
   const bool pool = !p.lane_kernel && pool_kernel_eligible(p);
@@ -741,6 +752,25 @@ rtx_status rtx_scene_render_device(rtx_scene* s, uint32_t width, uint32_t height
   uint32_t launches = 0;
   const rtx_status st = render_common(s, width, height, seed, flags, shard, (double*)d_out_rgb, (uint32_t*)d_out_primary_hit_id,
                                       (unsigned long long*)d_out_counters, wc, (cudaStream_t)cuda_stream, &launches);
+  s->last_launches = launches;
+  return st;
+}
+
+rtx_status rtx_scene_render_device_band(rtx_scene* s, uint32_t width, uint32_t height, uint64_t seed, uint32_t flags,
+                                        const rtx_shard* shard, uint32_t tile_row_first, uint32_t tile_row_count,
+                                        void* d_out_rgb, void* d_out_primary_hit_id, void* d_out_counters,
+                                        void* cuda_stream) {
+  if (!s) return fail(s, RTX_ERR_INVALID_ARGUMENT, "null scene");
+  if (!d_out_rgb && !(flags & RTX_FLAG_NO_RADIANCE) && !d_out_primary_hit_id)
+    return fail(s, RTX_ERR_INVALID_ARGUMENT, "no output buffer");
+  std::lock_guard<std::mutex> lk(s->mu);
+  RTX_CUDA_TRY(s, cudaSetDevice(s->device));
+  static thread_local uint32_t slot = 0;
+  uint32_t* wc = s->d_work_counter + (slot++ & 63u);
+  uint32_t launches = 0;
+  const uint32_t rows[2] = {tile_row_first, tile_row_count};
+  const rtx_status st = render_common(s, width, height, seed, flags, shard, (double*)d_out_rgb, (uint32_t*)d_out_primary_hit_id,
+                                      (unsigned long long*)d_out_counters, wc, (cudaStream_t)cuda_stream, &launches, nullptr, rows);
   s->last_launches = launches;
   return st;
 }

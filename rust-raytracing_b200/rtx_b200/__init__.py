@@ -453,6 +453,16 @@ class Scene:
                                                        C.byref(sh) if sh is not None else None,
                                                        d_rgb, d_ids, d_counters, stream), h)
 
+    def render_device_band(self, width, height, seed, flags, shard, tile_row_first, tile_row_count, d_rgb, d_ids,
+                           d_counters, stream):
+        """render_device for the band of 16-pixel tile rows [tile_row_first, tile_row_first + tile_row_count) only."""
+        h = self._sync()
+        sh = Shard(*shard) if shard is not None else None
+        _abi.check(_abi.load().rtx_scene_render_device_band(h, width, height, seed, flags,
+                                                            C.byref(sh) if sh is not None else None,
+                                                            tile_row_first, tile_row_count, d_rgb, d_ids, d_counters,
+                                                            stream), h)
+
     @property
     def last_device_launches(self):
         """Kernels launched by the most recent render_device call."""

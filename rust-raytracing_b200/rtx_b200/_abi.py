@@ -111,6 +111,8 @@ SIGNATURES = {
     "rtx_scene_render": (C.c_int32, [_vp, C.c_uint32, C.c_uint32, C.c_uint64, C.c_uint32, _vp, _vp, _P(Stats)]),
     "rtx_scene_render_device": (C.c_int32, [_vp, C.c_uint32, C.c_uint32, C.c_uint64, C.c_uint32, _P(Shard),
                                             _vp, _vp, _vp, _vp]),
+    "rtx_scene_render_device_band": (C.c_int32, [_vp, C.c_uint32, C.c_uint32, C.c_uint64, C.c_uint32, _P(Shard),
+                                                 C.c_uint32, C.c_uint32, _vp, _vp, _vp, _vp]),
     "rtx_shard_tile_count": (C.c_uint64, [C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32]),
     "rtx_deinterleave_tiles": (C.c_int32, [C.c_uint32, C.c_uint32, C.c_uint32, _vp, _vp, _vp, _vp, _vp]),
     "rtx_scene_render_to_rgb8": (C.c_int32, [_vp, C.c_uint32, C.c_uint32, C.c_uint64, C.c_uint32, _vp, _P(Stats)]),

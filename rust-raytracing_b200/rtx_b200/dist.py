@@ -178,6 +178,41 @@ class PeerFrame:
         if self.world > 1:
             dist.all_reduce(self._token, group=self.group)
 
+    def band_rows(self, bands):
+        """Tile-row ranges [(first, end), ...] of `bands` bands; the last one is half as tall as the others (its
+        copy-out is the one nothing overlaps)."""
+        tiles_y = (self.height + RTX_TILE - 1) // RTX_TILE
+        bands = max(1, min(int(bands), tiles_y))
+        den = 2 * bands - 1
+        edges = [tiles_y * 2 * b // den for b in range(bands)] + [tiles_y]
+        return [(edges[b], edges[b + 1]) for b in range(bands) if edges[b + 1] > edges[b]]
+
+    def render_to_host(self, scene, seed, host_rgb, counters=None, flags=RTX_ACCEL_AUTO, bands=4):
+        """render() with the frame handed over to pinned host memory on the owner: the image is rendered in bands of
+        tile rows; after a band's completion barrier the owner's copy engine moves its rows to `host_rgb`
+        ([h][w][3] f64, pinned; None on the other ranks) while every rank is already rendering the next band.
+        Returns after the work is enqueued; synchronize the device before reading `host_rgb`."""
+        dev = torch.device("cuda", self.device)
+        cur = torch.cuda.current_stream(dev)
+        if self.owner and getattr(self, "_copy_stream", None) is None:
+            self._copy_stream = torch.cuda.Stream(device=dev)
+            self._frame_rgb = self.tensors()[0]
+        for (r0, r1) in self.band_rows(bands):
+            scene.render_device_band(self.width, self.height, seed, flags | _abi.RTX_FLAG_SHARD_IN_PLACE,
+                                     (self.rank, self.world), r0, r1 - r0, self.rgb_ptr, self.ids_ptr,
+                                     counters.data_ptr() if counters is not None else None, cur.cuda_stream)
+            if self.world > 1:
+                dist.all_reduce(self._token, group=self.group)
+            if self.owner:
+                y0, y1 = r0 * RTX_TILE, min(self.height, r1 * RTX_TILE)
+                ev = torch.cuda.Event()
+                ev.record(cur)
+                self._copy_stream.wait_event(ev)
+                with torch.cuda.stream(self._copy_stream):
+                    host_rgb[y0:y1].copy_(self._frame_rgb[y0:y1], non_blocking=True)
+        if self.owner:
+            cur.wait_stream(self._copy_stream)
+
     def close(self):
         lib = _abi.load()
         if self.ptr:

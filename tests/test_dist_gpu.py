@@ -31,6 +31,9 @@ def _worker(rank, world, port, w, h, q):
         rgb2, ids2, counters2, frame = rdist.render_distributed_p2p(sc, w, h, seed=3)
         total2 = counters2.clone()
         dist.all_reduce(total2)
+        # and once more handed over to pinned host memory band by band (PeerFrame.render_to_host)
+        pin = torch.full((h, w, 3), -1.0, dtype=torch.float64).pin_memory() if rank == 0 else None
+        frame.render_to_host(sc, 3, pin, bands=3)
         torch.cuda.synchronize()
         if rank == 0:
             full, ids_full = sc.render(w, h, seed=3, want_ids=True)
@@ -40,7 +43,8 @@ def _worker(rank, world, port, w, h, q):
             ok2 = rgb2.cpu().numpy().tobytes() == full.tobytes()
             ok2 = ok2 and np.array_equal(ids2.cpu().numpy().view(np.uint32), ids_full)
             ok2 = ok2 and int(total2[0].item()) == sc.last_stats.rays
-            q.put((bool(ok), bool(ok2)))
+            ok3 = pin.numpy().tobytes() == full.tobytes()
+            q.put((bool(ok), bool(ok2), bool(ok3)))
         dist.barrier()
         frame.close()
     finally:
@@ -63,4 +67,4 @@ def test_two_gpu_render_equals_one_gpu(rtx, gpu):
     for p in procs:
         p.join(300)
         assert p.exitcode == 0
-    assert q.get(timeout=5) == (True, True)  # (NCCL gather path, fused peer-store path)
+    assert q.get(timeout=5) == (True, True, True)  # (NCCL gather path, fused peer-store path, banded hand-over to the host)

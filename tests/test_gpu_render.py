@@ -333,3 +333,45 @@ def test_queue_plan_selection_and_launch_count(rtx, gpu):
     assert launches(s2, rtx.RTX_FLAG_SAMPLE_QUEUE) == 2
     big = scenes.random_spheres(n=300, rays_per_pixel=8, max_bounces=2)
     assert launches(big, rtx.RTX_ACCEL_LBVH) == 1
+
+
+def test_device_bands_compose_the_frame(rtx, gpu):
+    """rtx_scene_render_device_band: the bands of a frame, rendered one by one into the same buffers, give the bytes of
+    one whole-frame call — for the whole image and for every shard of a 3-way split (in place and compact), pool
+    kernel under both queue plans and the LBVH lane kernel; rows outside a band are left alone."""
+    import torch
+    from rtx_b200 import scenes
+    from rtx_b200 import dist as rdist
+    dev = torch.device("cuda", 0)
+    st = torch.cuda.current_stream(dev).cuda_stream
+    w, h = 333, 211  # 14 tile rows, ragged in both directions
+    cases = [(scenes.sphere_demo(rays_per_pixel=5, max_bounces=6), rtx.RTX_ACCEL_AUTO),
+             (scenes.sphere_demo(rays_per_pixel=5, max_bounces=6), rtx.RTX_FLAG_PIXEL_QUEUE),
+             (scenes.random_spheres(n=400, rays_per_pixel=2, max_bounces=3), rtx.RTX_ACCEL_LBVH)]
+    for sc, fl in cases:
+        for world in (1, 3):
+            for rank in range(world):
+                for in_place in ((True,) if world == 1 else (True, False)):
+                    f = fl | (rtx.RTX_FLAG_SHARD_IN_PLACE if in_place else 0)
+                    shard = (rank, world) if world > 1 else None
+                    if in_place:
+                        a = torch.full((h, w, 3), -7.0, dtype=torch.float64, device=dev)
+                        ia = torch.full((h, w), -7, dtype=torch.int32, device=dev)
+                    else:
+                        a, ia = rdist.alloc_shard_buffers(w, h, world, dev, want_ids=True)
+                        a.fill_(-7.0), ia.fill_(-7)
+                    b, ib = a.clone(), ia.clone()
+                    ca = torch.zeros(8, dtype=torch.int64, device=dev)
+                    cb = torch.zeros(8, dtype=torch.int64, device=dev)
+                    sc.render_device(w, h, 9, f, shard, a.data_ptr(), ia.data_ptr(), ca.data_ptr(), st)
+                    for (r0, n) in ((0, 5), (5, 1), (6, 0), (6, 7), (13, 40)):
+                        sc.render_device_band(w, h, 9, f, shard, r0, n, b.data_ptr(), ib.data_ptr(), cb.data_ptr(), st)
+                    torch.cuda.synchronize()
+                    assert torch.equal(a, b) and torch.equal(ia, ib), (fl, world, rank, in_place)
+                    assert torch.equal(ca[:4], cb[:4]), (fl, world, rank, in_place)
+    # a single band touches nothing outside its rows
+    sc = cases[0][0]
+    c = torch.full((h, w, 3), -7.0, dtype=torch.float64, device=dev)
+    sc.render_device_band(w, h, 9, rtx.RTX_ACCEL_AUTO, None, 2, 3, c.data_ptr(), None, None, st)
+    torch.cuda.synchronize()
+    assert bool((c[:32] == -7.0).all()) and bool((c[80:] == -7.0).all()) and bool((c[32:80] != -7.0).all())
