@@ -27,14 +27,11 @@ sys.path.insert(0, os.path.join(ROOT, "rust-raytracing_b200"))
 
 WIDTH, HEIGHT, SPP, MAX_BOUNCES, SEED = 1920, 1080, 64, 8, 1
 # one `ncu --set full` capture of render_pool_kernel<64,1,true,24> on this workload (profiles/r01_render_pool_kernel_v6_raw.csv)
-NCU_TRAFFIC = 34150912 + 3167205000
-NCU_TRAFFIC_SOURCE = ("bytes per launch, dram__bytes_read.sum 34.2 MB + dram__bytes_write.sum 3167.2 MB of one `ncu --set full` capture of "
-                      "render_pool_kernel<64,1,true,24> on this workload (profiles/r01_render_pool_kernel_v6_raw.csv): the sample "
-                      "queue's scratch, 24 B per camera path x 132.7 M paths = 3185 MB, written once; tail_sum_kernel then reads "
-                      "it once (3185 MB in 0.45 ms = 7.07 TB/s, profiles/r01_tail_sum_kernel_raw.csv); the 49.8 MB frame itself "
-                      "is written by tail_sum_kernel")
-METRIC = "Mrays/s at 1080p 64spp, 1/2/4/8 B200, vs ref CPU path on host cores"
-WORKLOAD = "S1 sphere demo scene (1 plane + 6 spheres), 1920x1080, 64 spp, max depth 8 (BASELINE.json configs[1])"
+NCU_TRAFFIC = 457520000 + 674960000
+NCU_TRAFFIC_SOURCE = ("bytes per launch, dram__bytes_read.sum 457.5 MB + dram__bytes_write.sum 675.0 MB of one ncu capture of "
+                      "render_pool_kernel<64,1,true,24> on this workload (profiles/r01_SUMMARY.md): the sample queue's scratch is a "
+                      "flag byte per camera path (132.7 MB) + 24 B of radiance for the 21 % of paths whose radiance is not zero; "
+                      "tail_sum_kernel then reads 1.27 GB in 0.235 ms (5.4 TB/s) and writes the 49.8 MB frame")
 
 
 def parse_args():
@@ -338,7 +335,7 @@ def run_b200(args):
     achieved = flops / (dev_ms * 1e-3) / 1e12
     per_rank = max(1, scene.last_device_launches)
     sample_queue = per_rank >= 2  # (granule, sample) entries: 24 B of scratch per camera path, written then summed
-    hbm_bytes = K * npix * 28 + (paths * 48 if sample_queue else 0)
+    hbm_bytes = K * npix * 28 + (paths * 2 if sample_queue else 0)  # + the non-zero paths' 2 x 24 B (scene dependent)
     peaks = {}
     try:
         peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))

@@ -84,9 +84,15 @@ __global__ void __launch_bounds__(256) tail_sum_kernel(const __grid_constant__ R
   granule_pixel(p, g, k, &x, &y, &out_index);
   const uint32_t rpp = (uint32_t)p.rays_per_pixel;
   V3 acc = mk3(0.0, 0.0, 0.0);
-  const double* src = p.tail_scratch + ((size_t)tg * rpp * GRAN_PIXELS + k) * 3;
+  const size_t slot0 = (size_t)tg * rpp * GRAN_PIXELS + k;
+  const double* src = p.tail_scratch + slot0 * 3;
+  // one flag byte per camera path, behind the values: 0 = the path's radiance was (+-)0 and its values were never
+  // written.  Skipping `acc + 0` is exact: acc starts at +0 and x + (+-0) == x for every x that can arise (a sum
+  // that starts at +0 is never -0).
+  const unsigned char* flag = reinterpret_cast<const unsigned char*>(p.tail_scratch + (size_t)p.tail_granules * rpp * GRAN_PIXELS * 3) + slot0;
 #pragma unroll 4
-  for (uint32_t s = 0; s < rpp; ++s, src += GRAN_PIXELS * 3) acc = acc + mk3(__ldcs(src), __ldcs(src + 1), __ldcs(src + 2));
+  for (uint32_t s = 0; s < rpp; ++s, src += GRAN_PIXELS * 3, flag += GRAN_PIXELS)
+    if (__ldcs(flag)) acc = acc + mk3(__ldcs(src), __ldcs(src + 1), __ldcs(src + 2));
   const V3 px = acc / (double)rpp;
   p.out_rgb[(size_t)out_index * 3 + 0] = px.x;
   p.out_rgb[(size_t)out_index * 3 + 1] = px.y;
@@ -217,8 +223,13 @@ __global__ void __launch_bounds__(POOL_WARPS * 32, MIN_BLOCKS) __maxnreg__(pool_
         if (end) {
           if (SAMPLE_QUEUE) {
             // single-sample context: this sample's radiance goes to the scratch, the context is free again
-            double* dst = p.tail_scratch + (size_t)(uint32_t)P.ldu(F_M3, slot) * 3;
-            dst[0] = res.x, dst[1] = res.y, dst[2] = res.z;  // (plain stores: __stcg's STG.STRONG.GPU cost 11 % of the kernel)
+            const size_t sslot = (size_t)(uint32_t)P.ldu(F_M3, slot);
+            const bool nonzero = !(res.x == 0.0 && res.y == 0.0 && res.z == 0.0);  // (NaN counts as non-zero)
+            reinterpret_cast<unsigned char*>(p.tail_scratch + (size_t)p.tail_granules * rpp * GRAN_PIXELS * 3)[sslot] = nonzero ? 1 : 0;
+            if (nonzero) {  // (plain stores: __stcg's STG.STRONG.GPU cost 11 % of the kernel)
+              double* dst = p.tail_scratch + sslot * 3;
+              dst[0] = res.x, dst[1] = res.y, dst[2] = res.z;
+            }
             P.stu(F_M2, slot, pack2(NO_PIXEL, 0));
             P.stu(F_M0, slot, 0);
           } else {
@@ -397,7 +408,7 @@ bool pool_kernel_eligible(const RenderParams& p) {
 // Auto: the sample queue when rpp >= 4 and the scratch fits the budget — except for a large frame rendered straight
 // into pinned host memory, where the pixel queue's overlapped stores win (C2 e2e 12.3 ms).
 // RTX_FLAG_PIXEL_QUEUE / RTX_FLAG_SAMPLE_QUEUE force one.  The image is the same either way.
-// Returns the scratch bytes needed (0 = pixel queue): [granules * rpp * 32 * 3] f64.
+// Returns the scratch bytes needed (0 = pixel queue): [granules * rpp * 32 * 3] f64 + [granules * rpp * 32] flag bytes.
 size_t pool_plan_tail(RenderParams& p, int sm_count) {
   const uint64_t granules = (uint64_t)p.my_tiles * GRANS_PER_TILE;
   p.tail_first = (uint32_t)granules;
@@ -415,7 +426,7 @@ size_t pool_plan_tail(RenderParams& p, int sm_count) {
   const bool large = granules * GRAN_PIXELS >= 10 * contexts;
   if (mode != 2 && large && p.out_is_host) return 0;
   const uint64_t cap_bytes = 4ull << 30;  // scratch budget
-  const uint64_t bytes = granules * rpp * GRAN_PIXELS * 24;
+  const uint64_t bytes = granules * rpp * GRAN_PIXELS * 25;  // 24 B of radiance + 1 flag byte per camera path
   if (bytes > cap_bytes || granules * rpp * GRAN_PIXELS > 0xFFFFFFFFull) return 0;
   p.tail_granules = (uint32_t)granules;
   p.tail_first = 0;
@@ -434,7 +445,7 @@ uint32_t pool_host_bands(const RenderParams& p, int sm_count) {
   if (bands > p.tiles_y) bands = p.tiles_y;
   // every band's scratch has to fit the budget of pool_plan_tail
   const uint64_t band_pixels = ((uint64_t)(p.tiles_y + bands - 1) / bands) * p.tiles_x * TILE * TILE;
-  if (band_pixels * p.rays_per_pixel * 24 > (4ull << 30)) return 1;
+  if (band_pixels * p.rays_per_pixel * 25 > (4ull << 30)) return 1;
   return bands < 1u ? 1u : bands;
 }
 
