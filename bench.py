@@ -32,6 +32,8 @@ NCU_TRAFFIC_SOURCE = ("bytes per launch, dram__bytes_read.sum 457.5 MB + dram__b
                       "render_pool_kernel<64,1,true,24> on this workload (profiles/r01_SUMMARY.md): the sample queue's scratch is a "
                       "flag byte per camera path (132.7 MB) + 24 B of radiance for the 21 % of paths whose radiance is not zero; "
                       "tail_sum_kernel then reads 1.27 GB in 0.235 ms (5.4 TB/s) and writes the 49.8 MB frame")
+METRIC = "Mrays/s at 1080p 64spp, 1/2/4/8 B200, vs ref CPU path on host cores"
+WORKLOAD = "S1 sphere demo scene (1 plane + 6 spheres), 1920x1080, 64 spp, max depth 8 (BASELINE.json configs[1])"
 
 
 def parse_args():

@@ -33,7 +33,7 @@ constexpr int POOL_WARP_SCRATCH = POOL_SLOTS_MAX;  // per warp: compaction indic
 constexpr uint32_t FULLMASK = 0xFFFFFFFFu;
 constexpr uint32_t NO_PIXEL = 0xFFFFFFFFu;
 // Sample queue: consecutive samples of a granule one queue entry covers (one atomic + one granule decode per entry)
-constexpr uint32_t SAMPLES_PER_ENTRY = 4;
+constexpr uint32_t SAMPLES_PER_ENTRY = 8;
 
 // Context fields, SoA per warp: word(f, slot) = pool[f * POOL_SLOTS + slot], 8 bytes each.  A pixel-queue
 // context keeps its pixel for all rpp samples (running sum + the pixel's focal point: 22 words); a sample-queue
