@@ -102,7 +102,7 @@ __global__ void __launch_bounds__(256) tail_sum_kernel(const __grid_constant__ R
 // Registers per thread that still let `warps` warps share an SM's 64 K registers (allocated 8 per thread at a time).
 constexpr int pool_max_regs(int warps) { return (65536 / (warps * 32)) / 8 * 8 > 128 ? 128 : (65536 / (warps * 32)) / 8 * 8; }
 
-template <int POOL_SLOTS, int MIN_BLOCKS, bool SAMPLE_QUEUE, int POOL_WARPS = 8>
+template <int POOL_SLOTS, int MIN_BLOCKS, bool SAMPLE_QUEUE, int POOL_WARPS = 8, bool HAS_TRI = true>
 __global__ void __launch_bounds__(POOL_WARPS * 32, MIN_BLOCKS) __maxnreg__(pool_max_regs(POOL_WARPS * MIN_BLOCKS)) render_pool_kernel(const __grid_constant__ RenderParams p) {
   constexpr int POOL_BLOCK = POOL_WARPS * 32;
   constexpr size_t POOL_BYTES_PER_WARP = Pool<POOL_SLOTS, SAMPLE_QUEUE>::BYTES_PER_WARP;
@@ -187,7 +187,7 @@ __global__ void __launch_bounds__(POOL_WARPS * 32, MIN_BLOCKS) __maxnreg__(pool_
           end = true;  // scene.rs:224-226
           res = P.ld3(F_RES, slot);
         } else {
-          const Hit h = closest_brute(sc, pos, dir, &n_panics);
+          const Hit h = closest_brute<HAS_TRI>(sc, pos, dir, &n_panics);
           ++n_rays;
           if (segment == 0 && sample == 0 && p.out_ids) p.out_ids[(uint32_t)P.ldu(F_M1, slot)] = h.id;
           res = P.ld3(F_RES, slot);
@@ -328,7 +328,7 @@ __global__ void __launch_bounds__(POOL_WARPS * 32, MIN_BLOCKS) __maxnreg__(pool_
             P.st3(F_ACC, slot, mk3(0.0, 0.0, 0.0));  // iter_ops.rs:4-8: the fold starts from zeros()
           if (p.out_ids && g_sample == 0) p.out_ids[out_index] = MISS_ID;
           need = false;
-          if (rpp == 0) {  // avg of an empty iterator: zeros / 0.0 = NaN (scene.rs:253-259)
+          if (!SAMPLE_QUEUE && rpp == 0) {  // avg of an empty iterator: zeros / 0.0 = NaN (scene.rs:253-259); the sample queue needs rpp >= 1
             if (p.out_rgb) {
               const V3 px = mk3(0.0, 0.0, 0.0) / (double)rpp;
               p.out_rgb[(size_t)out_index * 3 + 0] = px.x;
@@ -456,7 +456,7 @@ static size_t pool_smem_bytes(uint32_t blob_bytes) {
   return pools_off + POOL_WARPS * Pool<POOL_SLOTS, SAMPLE_QUEUE>::BYTES_PER_WARP + POOL_WARPS * POOL_WARP_SCRATCH + 440 * sizeof(double);
 }
 
-template <int POOL_SLOTS, int MIN_BLOCKS, bool SAMPLE_QUEUE, int POOL_WARPS = 8>
+template <int POOL_SLOTS, int MIN_BLOCKS, bool SAMPLE_QUEUE, int POOL_WARPS = 8, bool HAS_TRI = true>
 static cudaError_t launch_pool_variant(const RenderParams& p, int sm_count, cudaStream_t stream, uint32_t* out_launches) {
   constexpr int POOL_BLOCK = POOL_WARPS * 32;
   const size_t smem = pool_smem_bytes<POOL_SLOTS, SAMPLE_QUEUE, POOL_WARPS>(p.layout.bytes);
@@ -471,9 +471,9 @@ static cudaError_t launch_pool_variant(const RenderParams& p, int sm_count, cuda
   uint64_t want_blocks = (total_work + per_block - 1) / per_block;
   uint64_t grid = (uint64_t)sm_count * MIN_BLOCKS;
   if (want_blocks < grid) grid = want_blocks ? want_blocks : 1;
-  e = cudaFuncSetAttribute(render_pool_kernel<POOL_SLOTS, MIN_BLOCKS, SAMPLE_QUEUE, POOL_WARPS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  e = cudaFuncSetAttribute(render_pool_kernel<POOL_SLOTS, MIN_BLOCKS, SAMPLE_QUEUE, POOL_WARPS, HAS_TRI>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return e;
-  render_pool_kernel<POOL_SLOTS, MIN_BLOCKS, SAMPLE_QUEUE, POOL_WARPS><<<(unsigned)grid, POOL_BLOCK, smem, stream>>>(p);
+  render_pool_kernel<POOL_SLOTS, MIN_BLOCKS, SAMPLE_QUEUE, POOL_WARPS, HAS_TRI><<<(unsigned)grid, POOL_BLOCK, smem, stream>>>(p);
   if (out_launches) *out_launches += 1;
   e = cudaGetLastError();
   if (e != cudaSuccess || p.tail_granules == 0) return e;
@@ -496,6 +496,15 @@ static size_t pool_smem_optin() {
 // contexts, 80 registers) warps on an SM, all with 64 contexts per warp; they need almost all of the SM's shared
 // memory, so scenes whose blob does not fit next to the pools use the 2 x 8-warp variant.  Measured on C2
 // (profiles/r01_SUMMARY.md): 2 x 8 warps 13.00 ms, 1 x 20 warps 12.20 ms.
+// The kernel is specialised on what the scene holds: without triangles the triangle loop, its divisions and — what
+// matters — its registers are compiled out; at the 80-register cap of the 24-warp variant that alone is 6 % (C2 10.82
+// -> 10.20 ms: fewer rematerialised values, 2784 -> 2480 instructions, a smaller loop in the instruction cache).
+template <int POOL_SLOTS, int MIN_BLOCKS, bool SAMPLE_QUEUE, int POOL_WARPS>
+static cudaError_t launch_pool_for_scene(const RenderParams& p, int sm_count, cudaStream_t stream, uint32_t* out_launches) {
+  return p.layout.n_tri == 0 ? launch_pool_variant<POOL_SLOTS, MIN_BLOCKS, SAMPLE_QUEUE, POOL_WARPS, false>(p, sm_count, stream, out_launches)
+                             : launch_pool_variant<POOL_SLOTS, MIN_BLOCKS, SAMPLE_QUEUE, POOL_WARPS, true>(p, sm_count, stream, out_launches);
+}
+
 cudaError_t launch_render_pool(const RenderParams& p, int sm_count, cudaStream_t stream, uint32_t* out_launches) {
   // RTX_POOL_VARIANT (measurement knob): 0 = auto; 1 = 2 CTAs x 8 warps; 2 = 1 x 20 warps; 3 = 1 x 24 warps (sample queue only)
   static const int variant = [] { const char* v = getenv("RTX_POOL_VARIANT"); return v ? atoi(v) : 0; }();
@@ -503,14 +512,14 @@ cudaError_t launch_render_pool(const RenderParams& p, int sm_count, cudaStream_t
   const uint32_t blob = p.layout.bytes;
   if (p.tail_granules != 0) {  // sample queue
     if ((variant == 0 || variant == 3) && pool_smem_bytes<64, true, 24>(blob) <= optin)
-      return launch_pool_variant<64, 1, true, 24>(p, sm_count, stream, out_launches);
+      return launch_pool_for_scene<64, 1, true, 24>(p, sm_count, stream, out_launches);
     if ((variant == 0 || variant == 2) && pool_smem_bytes<64, true, 20>(blob) <= optin)
-      return launch_pool_variant<64, 1, true, 20>(p, sm_count, stream, out_launches);
-    return launch_pool_variant<64, 2, true, 8>(p, sm_count, stream, out_launches);
+      return launch_pool_for_scene<64, 1, true, 20>(p, sm_count, stream, out_launches);
+    return launch_pool_for_scene<64, 2, true, 8>(p, sm_count, stream, out_launches);
   }
   if ((variant == 0 || variant == 2) && pool_smem_bytes<64, false, 20>(blob) <= optin)
-    return launch_pool_variant<64, 1, false, 20>(p, sm_count, stream, out_launches);
-  return launch_pool_variant<64, 2, false, 8>(p, sm_count, stream, out_launches);
+    return launch_pool_for_scene<64, 1, false, 20>(p, sm_count, stream, out_launches);
+  return launch_pool_for_scene<64, 2, false, 8>(p, sm_count, stream, out_launches);
 }
 
 }  // namespace rtx

@@ -246,6 +246,8 @@ RTX_D bool sphere_cull_keep(const float* __restrict__ rec32, const SphereCull& k
 }
 
 // scene.rs:243-251 — brute-force scan over all three shape arrays.
+// HAS_TRI = false: the caller knows the scene has no triangles (the loop and its registers are compiled out)
+template <bool HAS_TRI = true>
 RTX_D Hit closest_brute(const SceneView& sc, V3 pos, V3 dir, uint32_t* panics) {
   Hit h;
   h.t = CUDART_INF;
@@ -276,7 +278,7 @@ RTX_D Hit closest_brute(const SceneView& sc, V3 pos, V3 dir, uint32_t* panics) {
     double t;
     if (plane_distance(sc.pl + (size_t)i * PL_STRIDE, pos, ri, &t)) consider(h, t, sc.pl_id[i], REF_PLANE | i);
   }
-  for (uint32_t i = 0; i < sc.n_tri; ++i) {
+  for (uint32_t i = 0; HAS_TRI && i < sc.n_tri; ++i) {
     double t;
     bool panic = false;
     if (triangle_distance(sc.tri + (size_t)i * TRI_STRIDE, pos, dir, ri, &t, &panic))
