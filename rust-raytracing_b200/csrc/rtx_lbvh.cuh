@@ -170,12 +170,13 @@ RTX_D bool box_test_prism(const float* lo, const float* hi, const RayF32& r, con
   return !(tnear > u);
 }
 
-template <bool PRISM>
+// HAS_TRI = false: the caller knows the scene has no triangles, so every leaf is a sphere
+template <bool PRISM, bool HAS_TRI = true>
 RTX_D void bvh_leaf_test(const SceneView& sc, uint32_t child, V3 pos, V3 dir, const RayInv& ri, Hit& h,
                          uint32_t* panics) {
   const uint32_t idx = child & WIDE_IDX;
   double t;
-  if (!(child & WIDE_TRI)) {
+  if (!HAS_TRI || !(child & WIDE_TRI)) {
     if (sphere_distance(sc.sph + (size_t)idx * SPH_STRIDE, pos, ri, &t))
       consider(h, t, sc.sph_id[idx], REF_SPHERE | idx);
   } else {
@@ -213,7 +214,7 @@ RTX_D bool bvh_pop(const uint32_t* stack_ref, const float* stack_t, int& sp, dou
 }
 
 // AXIS < 0: the 3-D tree; AXIS = 0..2: the prism tree that drops that axis.
-template <int AXIS>
+template <int AXIS, bool HAS_TRI = true>
 RTX_D void bvh_walk(const WideNode* __restrict__ nodes, const SceneView& sc, V3 pos, V3 dir, const RayInv& ri,
                     const RayF32& rf, const PrismRay& pr, Hit& h, uint32_t* panics, TraversalCounters& tc) {
   constexpr bool PRISM = AXIS >= 0;
@@ -225,9 +226,9 @@ RTX_D void bvh_walk(const WideNode* __restrict__ nodes, const SceneView& sc, V3 
   for (;;) {
     for (;;) {
       if (cur & WIDE_LEAF) {
-        if (cur & WIDE_TRI) break;
+        if (HAS_TRI && (cur & WIDE_TRI)) break;
         ++tc.prims;
-        bvh_leaf_test<PRISM>(sc, cur, pos, dir, ri, h, panics);
+        bvh_leaf_test<PRISM, HAS_TRI>(sc, cur, pos, dir, ri, h, panics);
         if (!bvh_pop(stack_ref, stack_t, sp, h.t, cur)) return;
         continue;
       }
@@ -259,13 +260,16 @@ RTX_D void bvh_walk(const WideNode* __restrict__ nodes, const SceneView& sc, V3 
       }
     }
     ++tc.prims;
-    bvh_leaf_test<PRISM>(sc, cur, pos, dir, ri, h, panics);
+    bvh_leaf_test<PRISM, HAS_TRI>(sc, cur, pos, dir, ri, h, panics);
     if (!bvh_pop(stack_ref, stack_t, sp, h.t, cur)) return;
   }
 }
 
 // scene.rs:243-251 through the trees: planes (unbounded, kept outside) by scan, then the 3-D tree, then the
 // prism trees.  Same Hit as closest_brute for every ray.
+// HAS_TRI = false (sphere-only scenes, e.g. C3): the prism trees, the triangle leaf test and their registers are
+// compiled out.
+template <bool HAS_TRI = true>
 RTX_D Hit closest_lbvh(const SceneView& sc, const BvhView& bv, V3 pos, V3 dir, uint32_t* panics,
                        TraversalCounters& tc) {
   Hit h;
@@ -282,7 +286,8 @@ RTX_D Hit closest_lbvh(const SceneView& sc, const BvhView& bv, V3 pos, V3 dir, u
   const RayF32 rf = make_ray_f32(pos, ri.dn);
   PrismRay pr;
   pr.den = 0.0f, pr.s = 1.0f, pr.z = 0.0f;
-  if (bv.root[0] != BVH_END) bvh_walk<-1>(bv.nodes[0], sc, pos, dir, ri, rf, pr, h, panics, tc);
+  if (bv.root[0] != BVH_END) bvh_walk<-1, HAS_TRI>(bv.nodes[0], sc, pos, dir, ri, rf, pr, h, panics, tc);
+  if (!HAS_TRI) return h;
   if (bv.root[1] != BVH_END) {
     pr = make_prism_ray<0>(bv, pos, ri.dn);
     bvh_walk<0>(bv.nodes[1], sc, pos, dir, ri, rf, pr, h, panics, tc);

@@ -34,7 +34,7 @@ constexpr int RENDER_BLOCK = 256;
 constexpr int BVH_BLOCKS_PER_SM = RTX_BVH_BLOCKS_PER_SM;
 constexpr uint32_t FULL = 0xFFFFFFFFu;
 
-template <bool SMEM_SCENE, bool USE_BVH>
+template <bool SMEM_SCENE, bool USE_BVH, bool HAS_TRI = true>
 __global__ void __launch_bounds__(RENDER_BLOCK, USE_BVH ? BVH_BLOCKS_PER_SM : 2) render_megakernel(const __grid_constant__ RenderParams p) {
   extern __shared__ __align__(128) unsigned char smem_raw[];
   const unsigned char* base = p.scene_blob;
@@ -155,7 +155,7 @@ __global__ void __launch_bounds__(RENDER_BLOCK, USE_BVH ? BVH_BLOCKS_PER_SM : 2)
       if (sc.n_obj == 0) {
         end = true;  // scene.rs:224-226
       } else {
-        const Hit h = USE_BVH ? closest_lbvh(sc, p.bvh, pos, dir, &n_panics, tc) : closest_brute(sc, pos, dir, &n_panics);
+        const Hit h = USE_BVH ? closest_lbvh<HAS_TRI>(sc, p.bvh, pos, dir, &n_panics, tc) : closest_brute<HAS_TRI>(sc, pos, dir, &n_panics);
         ++n_rays;
         if (segment == 0 && sample == 0 && p.out_ids) p.out_ids[out_index] = h.id;
         if (h.id == MISS_ID) {
@@ -244,10 +244,14 @@ cudaError_t launch_render(const RenderParams& p, int sm_count, cudaStream_t stre
     kernel<<<(unsigned)grid, RENDER_BLOCK, smem, stream>>>(p);
     return cudaSuccess;
   };
+  // specialised on triangle-free scenes (C3): the triangle code and its registers are compiled out
+  const bool tri = p.layout.n_tri != 0;
   if (use_smem)
-    e = p.use_bvh ? launch(render_megakernel<true, true>) : launch(render_megakernel<true, false>);
+    e = p.use_bvh ? (tri ? launch(render_megakernel<true, true, true>) : launch(render_megakernel<true, true, false>))
+                  : (tri ? launch(render_megakernel<true, false, true>) : launch(render_megakernel<true, false, false>));
   else
-    e = p.use_bvh ? launch(render_megakernel<false, true>) : launch(render_megakernel<false, false>);
+    e = p.use_bvh ? (tri ? launch(render_megakernel<false, true, true>) : launch(render_megakernel<false, true, false>))
+                  : (tri ? launch(render_megakernel<false, false, true>) : launch(render_megakernel<false, false, false>));
   if (e != cudaSuccess) return e;
   if (out_launches) *out_launches += 1;
   return cudaGetLastError();
