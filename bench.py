@@ -175,6 +175,11 @@ def run_b200(args):
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     if world != args.gpus:
         raise SystemExit(f"--gpus {args.gpus} but WORLD_SIZE={world}: launch N>1 with torch.distributed.run")
+    # stdout carries ONE JSON line: whatever libraries write to file descriptor 1 meanwhile (NCCL's version banner at
+    # communicator creation, build output) goes to stderr; the descriptor is restored for the final print
+    sys.stdout.flush()
+    saved_stdout = os.dup(1)
+    os.dup2(2, 1)
     if rank == 0:
         g.build()
     if not torch.cuda.is_available():
@@ -369,6 +374,8 @@ def run_b200(args):
     # under the sample queue) x ranks, + de-interleave on rank 0 with --gather nccl; NCCL's kernels are not ours
     per_rank = max(1, scene.last_device_launches)
     launches_per_step = world * per_rank if (world == 1 or args.gather == "p2p") else world * per_rank + 1
+    sys.stdout.flush()
+    os.dup2(saved_stdout, 1)
     print(json.dumps({
         "metric": METRIC, "value": value, "unit": "Mrays/s", "n_gpus": world, "steps": K, "warmup": WU,
         "ms_per_step": dev_ms / K, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
@@ -382,7 +389,7 @@ def run_b200(args):
                    "rays_per_step": rays_per_step, "hits_per_step": hits // K, "paths_per_step": paths // K},
         "e2e": e2e, "gpu_launches": launches_per_step * K, "roofline": roofline, "cpu_baseline": cpu_baseline,
         "clocks": clocks, "wall_s_timed_region": t_wall, "triangle_panics": panics,
-    }))
+    }), flush=True)
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
