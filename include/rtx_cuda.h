@@ -184,6 +184,12 @@ rtx_status rtx_scene_render_device_band(rtx_scene* scene, uint32_t width, uint32
                                         void* cuda_stream);
 /* Number of tiles (and therefore compact-buffer slots) shard `index` of `count` owns. */
 uint64_t   rtx_shard_tile_count(uint32_t width, uint32_t height, uint32_t index, uint32_t count);
+/* The local tiles (first, count — indices into the shard's tile list, which is also the order of its compact
+ * buffer) that rtx_scene_render_device_band renders for the tile rows [tile_row_first, tile_row_first +
+ * tile_row_count) of shard `index` of `count`.  Pure arithmetic; no device needed.                        */
+void       rtx_shard_band_tiles(uint32_t width, uint32_t height, uint32_t index, uint32_t count,
+                                uint32_t tile_row_first, uint32_t tile_row_count,
+                                uint32_t* out_first_local_tile, uint32_t* out_tile_count);
 /* Scatter gathered compact shard buffers (rank-major: [count][slots][RTX_TILE][RTX_TILE][...]) into
  * the full image layout on the device.  ≙ the row-ordered join of scene.rs:167-169.  Either pair of
  * pointers may be NULL.  slots = rtx_shard_tile_count(width, height, 0, count).                     */

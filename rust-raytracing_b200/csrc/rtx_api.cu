@@ -205,6 +205,21 @@ static uint64_t shard_tiles(uint32_t width, uint32_t height, uint32_t index, uin
   return (tiles - index + count - 1) / count;
 }
 
+// The band of tile rows [row_first, row_first + row_count) as a range of a shard's LOCAL tiles: tile t of the image
+// belongs to shard t mod count as its local tile t div count, so a contiguous range of image tiles is a contiguous
+// range of local tiles.  Rows beyond the image are clipped.
+static void shard_band_tiles(uint32_t width, uint32_t height, uint32_t index, uint32_t count, uint32_t row_first,
+                             uint32_t row_count, uint32_t* first, uint32_t* n) {
+  *first = 0, *n = 0;
+  if (count == 0 || index >= count) return;
+  const uint64_t tiles_x = (width + TILE - 1) / TILE, tiles_y = (height + TILE - 1) / TILE;
+  const uint64_t lo = std::min<uint64_t>(row_first, tiles_y) * tiles_x;
+  const uint64_t hi = std::min<uint64_t>((uint64_t)row_first + row_count, tiles_y) * tiles_x;
+  auto local_below = [&](uint64_t g) { return g > index ? (g - index + count - 1) / count : 0ull; };  // local tiles with image index < g
+  *first = (uint32_t)local_below(lo);
+  *n = (uint32_t)(local_below(hi) - local_below(lo));
+}
+
 // ---- small device kernels owned by the API layer ------------------------------------------------
 // ≙ the row-ordered join of scene.rs:167-169: scatter gathered per-rank tile buffers into the image.
 __global__ void deinterleave_kernel(uint32_t width, uint32_t height, uint32_t tiles_x, uint32_t count,
@@ -325,11 +340,7 @@ static rtx_status render_common(rtx_scene* s, uint32_t width, uint32_t height, u
   if (tile_rows) {
     // tile t of the image belongs to shard t mod count as its local tile t div count: a band of tile rows is a
     // contiguous range of local tiles
-    const uint64_t lo = std::min<uint64_t>((uint64_t)tile_rows[0], p.tiles_y) * p.tiles_x;
-    const uint64_t hi = std::min<uint64_t>((uint64_t)tile_rows[0] + tile_rows[1], p.tiles_y) * p.tiles_x;
-    auto local_below = [&](uint64_t g) { return g > sh.index ? (g - sh.index + sh.count - 1) / sh.count : 0ull; };
-    p.tile_first = (uint32_t)local_below(lo);
-    p.my_tiles = (uint32_t)(local_below(hi) - local_below(lo));
+    shard_band_tiles(width, height, sh.index, sh.count, tile_rows[0], tile_rows[1], &p.tile_first, &p.my_tiles);
   }
   if (p.my_tiles == 0) return RTX_OK;
   p.tail_first = p.my_tiles * GRANS_PER_TILE, p.tail_granules = 0, p.tail_scratch = nullptr, p.tail_done = nullptr;
@@ -733,6 +744,14 @@ rtx_status rtx_scene_clear_objects(rtx_scene* s) {
   return RTX_OK;
 }
 uint64_t rtx_scene_object_count(const rtx_scene* s) { return s ? s->n_obj : 0; }
+
+void rtx_shard_band_tiles(uint32_t width, uint32_t height, uint32_t index, uint32_t count, uint32_t tile_row_first,
+                          uint32_t tile_row_count, uint32_t* out_first_local_tile, uint32_t* out_tile_count) {
+  uint32_t first = 0, n = 0;
+  shard_band_tiles(width, height, index, count, tile_row_first, tile_row_count, &first, &n);
+  if (out_first_local_tile) *out_first_local_tile = first;
+  if (out_tile_count) *out_tile_count = n;
+}
 
 uint64_t rtx_shard_tile_count(uint32_t width, uint32_t height, uint32_t index, uint32_t count) {
   return shard_tiles(width, height, index, count);

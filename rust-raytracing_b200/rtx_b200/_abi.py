@@ -113,6 +113,8 @@ SIGNATURES = {
                                             _vp, _vp, _vp, _vp]),
     "rtx_scene_render_device_band": (C.c_int32, [_vp, C.c_uint32, C.c_uint32, C.c_uint64, C.c_uint32, _P(Shard),
                                                  C.c_uint32, C.c_uint32, _vp, _vp, _vp, _vp]),
+    "rtx_shard_band_tiles": (None, [C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32,
+                                    _P(C.c_uint32), _P(C.c_uint32)]),
     "rtx_shard_tile_count": (C.c_uint64, [C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32]),
     "rtx_deinterleave_tiles": (C.c_int32, [C.c_uint32, C.c_uint32, C.c_uint32, _vp, _vp, _vp, _vp, _vp]),
     "rtx_scene_render_to_rgb8": (C.c_int32, [_vp, C.c_uint32, C.c_uint32, C.c_uint64, C.c_uint32, _vp, _P(Stats)]),

@@ -94,6 +94,8 @@ extern "C" {
     pub fn rtx_scene_render_device_band(scene: *mut rtx_scene, width: u32, height: u32, seed: u64, flags: u32, shard: *const rtx_shard,
                                         tile_row_first: u32, tile_row_count: u32, d_out_rgb: *mut c_void, d_out_ids: *mut c_void,
                                         d_out_counters: *mut c_void, stream: *mut c_void) -> rtx_status;
+    pub fn rtx_shard_band_tiles(width: u32, height: u32, index: u32, count: u32, tile_row_first: u32, tile_row_count: u32,
+                                out_first_local_tile: *mut u32, out_tile_count: *mut u32);
     pub fn rtx_scene_render_to_rgb8(scene: *mut rtx_scene, width: u32, height: u32, seed: u64, flags: u32,
                                     out_rgb8: *mut u8, out_stats: *mut rtx_stats) -> rtx_status;
     pub fn rtx_last_error(scene: *const rtx_scene) -> *const c_char;

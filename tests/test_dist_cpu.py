@@ -100,3 +100,45 @@ def test_tile_ownership_is_a_partition():
             owned = [len(range(r, tiles, world)) for r in range(world)]
             assert owned == [int(shard_tile_count(w, h, r, world)) for r in range(world)]
             assert sum(owned) == tiles
+
+
+def test_band_tiles_match_enumeration():
+    """rtx_shard_band_tiles (the arithmetic behind rtx_scene_render_device_band): the local tiles of shard r of N whose
+    image tile lies in the tile rows [first, first + count) — compared with plain enumeration, including empty bands,
+    bands running past the image and degenerate shards; the bands of PeerFrame.band_rows tile every shard exactly."""
+    import ctypes as C
+    import types
+    sys.path.insert(0, os.path.join(ROOT, "rust-raytracing_b200"))
+    from rtx_b200 import _abi
+    from rtx_b200.dist import PeerFrame
+    lib = _abi.load()
+
+    def band(w, h, r, n, r0, cnt):
+        a, b = C.c_uint32(123), C.c_uint32(456)
+        lib.rtx_shard_band_tiles(w, h, r, n, r0, cnt, C.byref(a), C.byref(b))
+        return a.value, b.value
+
+    for (w, h) in ((72, 40), (333, 211), (1920, 1080), (17, 16), (16, 1)):
+        tx, ty = (w + T - 1) // T, (h + T - 1) // T
+        for world in (1, 2, 3, 8):
+            for r in range(world):
+                mine = list(range(r, tx * ty, world))  # image tile index of local tile k
+                for (r0, cnt) in ((0, ty), (0, 1), (1, 2), (ty - 1, 1), (ty - 1, 5), (ty, 3), (2, 0), (0, 10**6)):
+                    lo, hi = min(r0, ty) * tx, min(r0 + cnt, ty) * tx
+                    want = [k for k, t in enumerate(mine) if lo <= t < hi]
+                    first, n = band(w, h, r, world, r0, cnt)
+                    assert n == len(want), (w, h, world, r, r0, cnt)
+                    assert n == 0 or first == want[0]
+                # the bands a PeerFrame hands out cover the shard's tiles once, in order
+                for bands in (1, 2, 4, 7, 100):
+                    rows = PeerFrame.band_rows(types.SimpleNamespace(height=h), bands)
+                    assert rows[0][0] == 0 and rows[-1][1] == ty
+                    assert all(a[1] == b[0] for a, b in zip(rows, rows[1:]))
+                    got, nxt = 0, 0
+                    for (a, b) in rows:
+                        first, n = band(w, h, r, world, a, b - a)
+                        assert n == 0 or first == nxt
+                        nxt += n
+                        got += n
+                    assert got == len(mine)
+    assert band(64, 64, 3, 2, 0, 4) == (0, 0) and band(64, 64, 0, 0, 0, 4) == (0, 0)  # invalid shards: nothing
