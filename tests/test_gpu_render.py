@@ -38,13 +38,16 @@ def test_sphere_demo_800x600_1spp(rtx, oracle, gpu):
     assert frac_exact > 0.9  # only paths that bounced (sin/cos) can differ at all
 
 
-@pytest.mark.parametrize("w,h", [(256, 256), (333, 77), (17, 5), (1, 1), (1920, 1080)])
+@pytest.mark.parametrize("w,h", [(256, 256), (333, 77), (17, 5), (1, 1), (512, 512), (1024, 1024), (1920, 1080),
+                                 (2048, 2048), (3840, 2160), (4096, 4096), (7680, 4320)])
 def test_primary_only_hit_ids_bit_exact(rtx, oracle, gpu, w, h):
-    """Config C5 regime: max_bounces = 0, 1 spp — no libm on the device path, so radiance is bit-exact too."""
+    """Config C5, the whole sweep of BASELINE.json configs[4] (256^2 ... 7680x4320) plus ragged sizes: max_bounces = 0,
+    1 spp — no libm on the device path, so radiance is bit-exact too (scene.rs:144-159, 213-222, 243-251)."""
     from rtx_b200 import scenes
     sc = scenes.sphere_demo(rays_per_pixel=1, max_bounces=0)
     rgb, ids, ref, err = _compare(rtx, oracle, sc, w, h, seed=1, spp_tol=0.0)
     assert rgb.tobytes() == ref["rgb"].tobytes()
+    del rgb
     ids_only = sc.render_ids(w, h, seed=1)
     assert np.array_equal(ids_only, ref["ids"])
 

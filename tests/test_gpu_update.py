@@ -23,7 +23,17 @@ def _same(a, b):
     return a[0].tobytes() == b[0].tobytes() and np.array_equal(a[1], b[1])
 
 
-def test_sphere_updates_refit_the_lbvh(rtx, gpu):
+def _equals_oracle(oracle, sc, img, w, h, seed):
+    """The updated scene's image against the CPU oracle's render of the scene's CURRENT host-side data (the object list
+    a reference user holds after mutating the shapes behind their Arc<Mutex<..>>, object.rs:12): primary hit ids and
+    ray count equal, every radiance byte equal."""
+    ref = oracle.render_scene(sc, w, h, seed=seed)
+    assert np.array_equal(img[1], ref["ids"]), f"{(img[1] != ref['ids']).sum()} primary hit ids differ from the oracle"
+    assert sc.last_stats.rays == ref["rays"], (sc.last_stats.rays, ref["rays"])
+    assert img[0].tobytes() == ref["rgb"].tobytes(), float(np.abs(img[0] - ref["rgb"]).max())
+
+
+def test_sphere_updates_refit_the_lbvh(rtx, oracle, gpu):
     from rtx_b200 import scenes
     LB, BR = rtx.RTX_ACCEL_LBVH, rtx.RTX_ACCEL_BRUTE
     sc = scenes.random_spheres(n=2000, rays_per_pixel=2, max_bounces=4)
@@ -42,6 +52,7 @@ def test_sphere_updates_refit_the_lbvh(rtx, gpu):
     after = sc.render(w, h, seed=3, flags=LB, want_ids=True)
     assert (sc.accel_builds, sc.accel_refits) == (1, 1), "the update must refit, not rebuild"
     assert not _same(before, after)
+    _equals_oracle(oracle, sc, after, w, h, 3)
     fresh = _fresh_like(rtx, sc)
     assert _same(after, fresh.render(w, h, seed=3, flags=LB, want_ids=True))
     assert _same(after, fresh.render(w, h, seed=3, flags=BR, want_ids=True))
@@ -49,12 +60,13 @@ def test_sphere_updates_refit_the_lbvh(rtx, gpu):
     sc.update_objects(idx[:10], new_shapes[:10] + 0.25)
     again = sc.render(w, h, seed=3, flags=LB, want_ids=True)
     assert (sc.accel_builds, sc.accel_refits) == (1, 2)
+    _equals_oracle(oracle, sc, again, w, h, 3)
     assert _same(again, _fresh_like(rtx, sc).render(w, h, seed=3, flags=BR, want_ids=True))
     sc.rebuild_accel()
     assert _same(again, sc.render(w, h, seed=3, flags=LB, want_ids=True)) and sc.accel_builds == 2
 
 
-def test_membership_change_falls_back_to_rebuild(rtx, gpu):
+def test_membership_change_falls_back_to_rebuild(rtx, oracle, gpu):
     from rtx_b200 import scenes
     LB = rtx.RTX_ACCEL_LBVH
     sc = scenes.random_spheres(n=500, rays_per_pixel=1, max_bounces=3)
@@ -65,10 +77,11 @@ def test_membership_change_falls_back_to_rebuild(rtx, gpu):
     sc.update_objects([7], bad[None, :])
     img = sc.render(160, 90, seed=1, flags=LB, want_ids=True)
     assert sc.accel_builds == 2
+    _equals_oracle(oracle, sc, img, 160, 90, 1)
     assert _same(img, _fresh_like(rtx, sc).render(160, 90, seed=1, flags=rtx.RTX_ACCEL_BRUTE, want_ids=True))
 
 
-def test_triangle_updates(rtx, gpu):
+def test_triangle_updates(rtx, oracle, gpu):
     from rtx_b200 import scenes
     LB, BR = rtx.RTX_ACCEL_LBVH, rtx.RTX_ACCEL_BRUTE
     sc = scenes.terrain(grid=25, rays_per_pixel=1, max_bounces=4)
@@ -83,6 +96,7 @@ def test_triangle_updates(rtx, gpu):
     sc.update_objects(idx, moved)
     img = sc.render(w, h, seed=2, flags=LB, want_ids=True)
     assert (sc.accel_builds, sc.accel_refits) == (1, 1)
+    _equals_oracle(oracle, sc, img, w, h, 2)
     fresh = _fresh_like(rtx, sc)
     assert _same(img, fresh.render(w, h, seed=2, flags=LB, want_ids=True))
     assert _same(img, fresh.render(w, h, seed=2, flags=BR, want_ids=True))
@@ -93,10 +107,11 @@ def test_triangle_updates(rtx, gpu):
     sc.update_objects([tri[3]], deg[None, :])
     img2 = sc.render(w, h, seed=2, flags=LB, want_ids=True)
     assert sc.accel_builds == 2
+    _equals_oracle(oracle, sc, img2, w, h, 2)
     assert _same(img2, _fresh_like(rtx, sc).render(w, h, seed=2, flags=BR, want_ids=True))
 
 
-def test_small_scene_partial_upload_and_planes(rtx, gpu):
+def test_small_scene_partial_upload_and_planes(rtx, oracle, gpu):
     """S1 (pool kernel, scanned from shared memory): updates travel as partial uploads of the scene blob."""
     from rtx_b200 import scenes
     sc = scenes.sphere_demo(rays_per_pixel=4, max_bounces=8)
@@ -106,6 +121,7 @@ def test_small_scene_partial_upload_and_planes(rtx, gpu):
     sc.update_objects([0], np.array([[0.0, 0.0, -0.2, 0.0, 0.1, 1.0]]))  # the ground plane, tilted
     b = sc.render(200, 120, seed=1, want_ids=True)
     assert not _same(a, b)
+    _equals_oracle(oracle, sc, b, 200, 120, 1)
     assert _same(b, _fresh_like(rtx, sc).render(200, 120, seed=1, want_ids=True))
 
 

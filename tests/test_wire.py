@@ -70,7 +70,7 @@ def test_decode_rejects_bad_input(rtx):
 
 
 @pytest.mark.gpu
-def test_wire_scene_renders_like_the_f32_rounded_scene(rtx, gpu):
+def test_wire_scene_renders_like_the_f32_rounded_scene(rtx, oracle, gpu):
     import ctypes as C
 
     from rtx_b200 import _abi, wire
@@ -94,6 +94,12 @@ def test_wire_scene_renders_like_the_f32_rounded_scene(rtx, gpu):
     ia, ida = a.render(200, 120, seed=4, want_ids=True)
     ib, idb = b.render(200, 120, seed=4, want_ids=True)
     assert ia.tobytes() == ib.tobytes() and np.array_equal(ida, idb) and np.isfinite(ia).all() and ia.any()
+    # ... and both equal the CPU oracle's render of the f32-rounded scene (each scene's own host-side object list is
+    # what the oracle is fed): ids, ray count, every radiance byte
+    for s_ in (a, b):
+        ref = oracle.render_scene(s_, 200, 120, seed=4)
+        assert np.array_equal(ida, ref["ids"]) and ia.tobytes() == ref["rgb"].tobytes()
+        assert s_.last_stats.rays == ref["rays"]
     # and straight through the C entry points on a raw handle
     lib = _abi.load()
     h = C.c_void_p()
