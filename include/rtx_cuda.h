@@ -182,6 +182,21 @@ rtx_status rtx_scene_render_device_band(rtx_scene* scene, uint32_t width, uint32
                                         const rtx_shard* shard, uint32_t tile_row_first, uint32_t tile_row_count,
                                         void* d_out_rgb, void* d_out_primary_hit_id, void* d_out_counters,
                                         void* cuda_stream);
+/* The whole-image rtx_scene_render_device for callers that cannot allocate device memory (CUDA graph capture,
+ * tight serving loops, harnesses that forbid cudaMalloc).  NO COUNTERPART IN THE REFERENCE.
+ * It runs the sample-queue kernel pair, whose scratch (work counter + 25 bytes per camera
+ * path: pixels rounded up to whole 16x16 tiles x rays_per_pixel) lives in a static device array of
+ * RTX_NOALLOC_SCRATCH_BYTES that every GPU which loads the library holds until exit; the call performs no
+ * cudaMalloc / cudaFree.  Preconditions, else RTX_ERR_INVALID_ARGUMENT with a message: the scene is already
+ * resident and has camera tables for this width/height/fov (one earlier render at this size through
+ * rtx_scene_render_device during set-up — that one allocates), it is a scanned scene (RTX_ACCEL_BRUTE applies;
+ * packed scene <= 16 KB), 1 <= rays_per_pixel, and the frame's scratch fits.  flags: RTX_ACCEL_AUTO/BRUTE,
+ * RTX_FLAG_SAMPLE_QUEUE.  Output bytes equal rtx_scene_render_device's.  All calls on one GPU share the static
+ * array: calls that overlap on the GPU (other streams, other scenes) race — the caller orders them.           */
+#define RTX_NOALLOC_SCRATCH_BYTES 33554432u   /* 32 MiB */
+rtx_status rtx_scene_render_device_noalloc(rtx_scene* scene, uint32_t width, uint32_t height, uint64_t seed,
+                                           uint32_t flags, void* d_out_rgb, void* d_out_primary_hit_id,
+                                           void* cuda_stream);
 /* Number of tiles (and therefore compact-buffer slots) shard `index` of `count` owns. */
 uint64_t   rtx_shard_tile_count(uint32_t width, uint32_t height, uint32_t index, uint32_t count);
 /* The local tiles (first, count — indices into the shard's tile list, which is also the order of its compact

@@ -453,6 +453,13 @@ class Scene:
                                                        C.byref(sh) if sh is not None else None,
                                                        d_rgb, d_ids, d_counters, stream), h)
 
+    def render_device_noalloc(self, width, height, seed, flags, d_rgb, d_ids, stream):
+        """rtx_scene_render_device_noalloc: whole-image device render whose scratch is the library's static device
+        array (no cudaMalloc/cudaFree in the call).  The scene must be resident and have been rendered once at this
+        size through render_device; raises RtxError otherwise, or when the frame's scratch exceeds the array."""
+        h = self._sync()
+        _abi.check(_abi.load().rtx_scene_render_device_noalloc(h, width, height, seed, flags, d_rgb, d_ids, stream), h)
+
     def render_device_band(self, width, height, seed, flags, shard, tile_row_first, tile_row_count, d_rgb, d_ids,
                            d_counters, stream):
         """render_device for the band of 16-pixel tile rows [tile_row_first, tile_row_first + tile_row_count) only."""

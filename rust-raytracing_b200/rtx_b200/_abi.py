@@ -77,6 +77,7 @@ RTX_FLAG_PIXEL_QUEUE = 32
 RTX_FLAG_SAMPLE_QUEUE = 64
 RTX_PEER_HANDLE_BYTES = 64
 RTX_TILE = 16
+RTX_NOALLOC_SCRATCH_BYTES = 32 << 20
 MISS_ID = 0xFFFFFFFF
 
 _vp = C.c_void_p
@@ -113,6 +114,7 @@ SIGNATURES = {
                                             _vp, _vp, _vp, _vp]),
     "rtx_scene_render_device_band": (C.c_int32, [_vp, C.c_uint32, C.c_uint32, C.c_uint64, C.c_uint32, _P(Shard),
                                                  C.c_uint32, C.c_uint32, _vp, _vp, _vp, _vp]),
+    "rtx_scene_render_device_noalloc": (C.c_int32, [_vp, C.c_uint32, C.c_uint32, C.c_uint64, C.c_uint32, _vp, _vp, _vp]),
     "rtx_shard_band_tiles": (None, [C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32,
                                     _P(C.c_uint32), _P(C.c_uint32)]),
     "rtx_shard_tile_count": (C.c_uint64, [C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32]),
