@@ -282,7 +282,7 @@ static T* mapped_device_pointer(T* host) {
 }
 
 // Fills RenderParams and launches.  Counters / outputs are device pointers.
-static rtx_status render_common(rtx_scene* s, uint32_t width, uint32_t height, uint64_t seed, uint32_t flags,
+static rtx_status render_common_on_stream(rtx_scene* s, uint32_t width, uint32_t height, uint64_t seed, uint32_t flags,
                                 const rtx_shard* shard, double* d_rgb, uint32_t* d_ids,
                                 unsigned long long* d_counters, uint32_t* d_work_counter, cudaStream_t stream,
                                 uint32_t* launches, double* host_rgb = nullptr, const uint32_t* tile_rows = nullptr) {
@@ -393,6 +393,29 @@ static rtx_status render_common(rtx_scene* s, uint32_t width, uint32_t height, u
   cudaError_t e = launch_render(p, s->sm_count, stream, launches);
   if (e != cudaSuccess) return cuda_fail(s, e, "render kernel launch");
   return RTX_OK;
+}
+
+// Renders of one scene share device state the scene owns — the sample queue's scratch, the band frame, the sin/cos
+// tables, the work counters — so they must not overlap on the GPU.  The host side is serialised by s->mu; the device
+// side by an event: every render records s->ev_last behind its last piece of work, and a render enqueued on a
+// DIFFERENT stream first makes that stream wait for it.  Two threads (or two streams) rendering one scene therefore
+// get correct frames, one after the other (≙ Scene::render(&self) being safe to call concurrently, scene.rs:144).
+static rtx_status render_common(rtx_scene* s, uint32_t width, uint32_t height, uint64_t seed, uint32_t flags,
+                                const rtx_shard* shard, double* d_rgb, uint32_t* d_ids, unsigned long long* d_counters,
+                                uint32_t* d_work_counter, cudaStream_t stream, uint32_t* launches, double* host_rgb = nullptr,
+                                const uint32_t* tile_rows = nullptr) {
+  if (!s->ev_last) RTX_CUDA_TRY(s, cudaEventCreateWithFlags(&s->ev_last, cudaEventDisableTiming));
+  if (s->last_valid && s->last_stream != stream) RTX_CUDA_TRY(s, cudaStreamWaitEvent(stream, s->ev_last, 0));
+  const rtx_status st = render_common_on_stream(s, width, height, seed, flags, shard, d_rgb, d_ids, d_counters, d_work_counter,
+                                                stream, launches, host_rgb, tile_rows);
+  // (also after a failure: whatever was enqueued before it is still in flight)
+  if (cudaEventRecord(s->ev_last, stream) == cudaSuccess) {
+    s->last_stream = stream;
+    s->last_valid = true;
+  } else {
+    cudaGetLastError();
+  }
+  return st;
 }
 
 }  // namespace rtx
@@ -560,6 +583,7 @@ rtx_status rtx_scene_destroy(rtx_scene* s) {
   cudaFree(s->d_rgb8);
   if (s->ev0) cudaEventDestroy(s->ev0);
   if (s->ev1) cudaEventDestroy(s->ev1);
+  if (s->ev_last) cudaEventDestroy(s->ev_last);
   if (s->stream) cudaStreamDestroy(s->stream);
   if (s->copy_stream) cudaStreamDestroy(s->copy_stream);
   for (cudaEvent_t ev : s->ev_band)
@@ -592,8 +616,8 @@ rtx_status rtx_scene_get_config(const rtx_scene* s, rtx_config* out) {
   return RTX_OK;
 }
 
+// (called with s->mu held: n_obj is read here)
 static rtx_status check_add(rtx_scene* s, const void* shapes, const void* materials, uint64_t n) {
-  if (!s) return fail(s, RTX_ERR_INVALID_ARGUMENT, "null scene");
   if (n && (!shapes || !materials)) return fail(s, RTX_ERR_INVALID_ARGUMENT, "null shapes/materials");
   if (s->n_obj + n >= (1ull << 30)) return fail(s, RTX_ERR_INVALID_ARGUMENT, "too many objects (limit 2^30)");
   return RTX_OK;
@@ -605,9 +629,10 @@ static void push_material(rtx_scene* s, const rtx_material& m) {
 }
 
 rtx_status rtx_scene_add_spheres(rtx_scene* s, const rtx_sphere* shapes, const rtx_material* materials, uint64_t n) {
+  if (!s) return fail(s, RTX_ERR_INVALID_ARGUMENT, "null scene");
+  std::lock_guard<std::mutex> lk(s->mu);
   rtx_status st = check_add(s, shapes, materials, n);
   if (st != RTX_OK) return st;
-  std::lock_guard<std::mutex> lk(s->mu);
   s->sph.reserve(s->sph.size() + n * SPH_STRIDE);
   for (uint64_t i = 0; i < n; ++i) {
     const size_t o = s->sph.size();
@@ -622,9 +647,10 @@ rtx_status rtx_scene_add_spheres(rtx_scene* s, const rtx_sphere* shapes, const r
   return RTX_OK;
 }
 rtx_status rtx_scene_add_planes(rtx_scene* s, const rtx_plane* shapes, const rtx_material* materials, uint64_t n) {
+  if (!s) return fail(s, RTX_ERR_INVALID_ARGUMENT, "null scene");
+  std::lock_guard<std::mutex> lk(s->mu);
   rtx_status st = check_add(s, shapes, materials, n);
   if (st != RTX_OK) return st;
-  std::lock_guard<std::mutex> lk(s->mu);
   for (uint64_t i = 0; i < n; ++i) {
     const size_t o = s->pl.size();
     s->pl.resize(o + PL_STRIDE);
@@ -638,9 +664,10 @@ rtx_status rtx_scene_add_planes(rtx_scene* s, const rtx_plane* shapes, const rtx
   return RTX_OK;
 }
 rtx_status rtx_scene_add_triangles(rtx_scene* s, const rtx_triangle* shapes, const rtx_material* materials, uint64_t n) {
+  if (!s) return fail(s, RTX_ERR_INVALID_ARGUMENT, "null scene");
+  std::lock_guard<std::mutex> lk(s->mu);
   rtx_status st = check_add(s, shapes, materials, n);
   if (st != RTX_OK) return st;
-  std::lock_guard<std::mutex> lk(s->mu);
   s->tri.reserve(s->tri.size() + n * TRI_STRIDE);
   for (uint64_t i = 0; i < n; ++i) {
     const size_t o = s->tri.size();
@@ -766,8 +793,7 @@ rtx_status rtx_scene_render_device(rtx_scene* s, uint32_t width, uint32_t height
     return fail(s, RTX_ERR_INVALID_ARGUMENT, "no output buffer");
   std::lock_guard<std::mutex> lk(s->mu);
   RTX_CUDA_TRY(s, cudaSetDevice(s->device));
-  static thread_local uint32_t slot = 0;
-  uint32_t* wc = s->d_work_counter + (slot++ & 63u);
+  uint32_t* wc = s->d_work_counter + (s->wc_slot++ & 63u);  // under s->mu
   uint32_t launches = 0;
   const rtx_status st = render_common(s, width, height, seed, flags, shard, (double*)d_out_rgb, (uint32_t*)d_out_primary_hit_id,
                                       (unsigned long long*)d_out_counters, wc, (cudaStream_t)cuda_stream, &launches);
@@ -784,8 +810,7 @@ rtx_status rtx_scene_render_device_band(rtx_scene* s, uint32_t width, uint32_t h
     return fail(s, RTX_ERR_INVALID_ARGUMENT, "no output buffer");
   std::lock_guard<std::mutex> lk(s->mu);
   RTX_CUDA_TRY(s, cudaSetDevice(s->device));
-  static thread_local uint32_t slot = 0;
-  uint32_t* wc = s->d_work_counter + (slot++ & 63u);
+  uint32_t* wc = s->d_work_counter + (s->wc_slot++ & 63u);  // under s->mu
   uint32_t launches = 0;
   const uint32_t rows[2] = {tile_row_first, tile_row_count};
   const rtx_status st = render_common(s, width, height, seed, flags, shard, (double*)d_out_rgb, (uint32_t*)d_out_primary_hit_id,

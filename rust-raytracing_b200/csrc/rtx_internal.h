@@ -77,6 +77,11 @@ struct rtx_scene {
 
   cudaStream_t stream = nullptr;  // used by the blocking host-buffer entry points
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+  // device-side ordering of renders of this scene that were enqueued on different streams (rtx_api.cu, render_common)
+  cudaEvent_t ev_last = nullptr;
+  cudaStream_t last_stream = nullptr;
+  bool last_valid = false;
+  uint32_t wc_slot = 0;  // next work-counter slot for the asynchronous entry points
   // banded host output (rtx_scene_render into pinned memory): a copy stream and one event per band + one for the end
   cudaStream_t copy_stream = nullptr;
   static constexpr uint32_t MAX_BANDS = 8;

@@ -1,6 +1,9 @@
 """Image-tile sharding across GPUs: one process per GPU (torch.distributed), no data-path collective
-while rendering, one gather of frame-buffer shards to rank 0 (NCCL over NVLink), then a de-interleave
-kernel.  ≙ the row threads + row-ordered join of Scene::render (raytracing/scene.rs:149-169).
+while rendering.  ≙ the row threads + row-ordered join of Scene::render (raytracing/scene.rs:149-169).
+The default assembly is PeerFrame (below): every rank's render kernel stores its finished pixels into rank
+0's frame over NVLink peer memory, and a 4-byte all-reduce is the completion barrier.  The NCCL path
+(render_distributed: compact shard buffers, one gather to rank 0, a de-interleave kernel) is kept as the A/B
+baseline.
 
 Ownership: the image is cut into RTX_TILE x RTX_TILE tiles numbered row-major; tile t belongs to rank
 t % world (interleaved, so sky tiles and object tiles spread evenly).  Each rank writes its tiles
@@ -121,7 +124,15 @@ class PeerFrame:
     """The full frame [h][w][3] f64 (+ [h][w] u32 ids) lives in rank `dst`'s HBM; every other rank maps it
     (rtx_peer_export / rtx_peer_open — cudaIpc) and its render kernel stores finished pixels at their final
     position through NVLink while it renders (RTX_FLAG_SHARD_IN_PLACE).  ≙ the row-ordered join of
-    scene.rs:167-169 without a gather step: the only collective left is the completion barrier."""
+    scene.rs:167-169 without a gather step: the only collective left is the completion barrier.
+
+    The frame is DOUBLE-BUFFERED: render k goes to buffer k & 1.  The barrier only tells the owner that the peers
+    have finished; nothing tells the peers that the owner has finished READING, and a peer starts its next render
+    as soon as its own barrier completes.  With two buffers the peers' render k+1 goes to the other buffer, and
+    their render k+2 starts after barrier k+1, which the owner enqueues on its stream behind everything it did with
+    frame k (its consumer kernels, or the wait on the copy stream that render_to_host ends with).  So: consume a
+    frame on the owner's CURRENT stream (or make that stream wait for the consumer) before calling render again.
+    All work is enqueued on torch's current stream of the device — NCCL's all-reduce runs there too."""
 
     def __init__(self, width, height, device, group=None, dst=0, want_ids=True):
         self.width, self.height, self.device, self.group, self.dst = width, height, int(device), group, dst
@@ -130,7 +141,9 @@ class PeerFrame:
         lib = _abi.load()
         self.rgb_bytes = width * height * 24
         self.ids_off = (self.rgb_bytes + 255) & ~255
-        total = self.ids_off + (width * height * 4 if want_ids else 0)
+        self.buf_bytes = (self.ids_off + (width * height * 4 if want_ids else 0) + 255) & ~255
+        total = 2 * self.buf_bytes
+        self._cur = 0  # buffer of the most recent render
         self.owner = self.rank == dst
         ptr = C.c_void_p()
         handle = torch.zeros(_abi.RTX_PEER_HANDLE_BYTES, dtype=torch.uint8)
@@ -147,8 +160,13 @@ class PeerFrame:
         if not self.owner:
             raw = (C.c_uint8 * _abi.RTX_PEER_HANDLE_BYTES).from_buffer_copy(bytes(handle.numpy().tobytes()))
             _abi.check(lib.rtx_peer_open(self.device, raw, C.byref(ptr)))
-        self.ptr = int(ptr.value)
+        self.base = int(ptr.value)
         self._token = torch.zeros(1, dtype=torch.int32, device=torch.device("cuda", self.device))
+
+    @property
+    def ptr(self):
+        """Device address of the buffer the most recent render went to."""
+        return self.base + self._cur * self.buf_bytes
 
     @property
     def rgb_ptr(self):
@@ -158,20 +176,32 @@ class PeerFrame:
     def ids_ptr(self):
         return self.ptr + self.ids_off if self.want_ids else None
 
+    def poison(self):
+        """Owner: fills BOTH buffers with NaN / 0xFFFFFFFE (stream-ordered) — a pixel no rank writes then shows in
+        any comparison (tests, bench.py's N-rank == 1-rank check).  Call on every rank; ends with a barrier so that
+        no peer store can precede the fill."""
+        dev = torch.device("cuda", self.device)
+        if self.owner:
+            raw = torch.as_tensor(_DevArray(self.base, (2 * self.buf_bytes // 8,), "<i8"), device=dev)
+            raw.fill_(-2)  # 0xFF..FE: a NaN as f64, 0xFFFFFFFE / 0xFFFFFFFF as ids
+        if self.world > 1:
+            dist.all_reduce(self._token, group=self.group)
+
     def tensors(self):
-        """torch views of the frame (valid on the owner; on peers they alias remote memory — do not read)."""
+        """torch views of the most recently rendered frame (valid on the owner until the next-but-one render; on
+        peers they alias remote memory — do not read)."""
         dev = torch.device("cuda", self.device)
         rgb = torch.as_tensor(_DevArray(self.ptr, (self.height, self.width, 3), "<f8"), device=dev)
         ids = torch.as_tensor(_DevArray(self.ptr + self.ids_off, (self.height, self.width), "<i4"),
                               device=dev) if self.want_ids else None
         return rgb, ids
 
-    def render(self, scene, seed, counters=None, flags=RTX_ACCEL_AUTO, stream=None):
+    def render(self, scene, seed, counters=None, flags=RTX_ACCEL_AUTO):
         """Every rank renders its tiles straight into the owner's frame, then a stream-ordered barrier:
         when it completes on the owner's stream every peer's kernel has finished, and a finished kernel's
-        stores are visible system-wide."""
-        if stream is None:
-            stream = torch.cuda.current_stream(torch.device("cuda", self.device)).cuda_stream
+        stores are visible system-wide.  Enqueued on torch's current stream."""
+        stream = torch.cuda.current_stream(torch.device("cuda", self.device)).cuda_stream
+        self._cur ^= 1
         scene.render_device(self.width, self.height, seed, flags | _abi.RTX_FLAG_SHARD_IN_PLACE,
                             (self.rank, self.world), self.rgb_ptr, self.ids_ptr,
                             counters.data_ptr() if counters is not None else None, stream)
@@ -196,7 +226,8 @@ class PeerFrame:
         cur = torch.cuda.current_stream(dev)
         if self.owner and getattr(self, "_copy_stream", None) is None:
             self._copy_stream = torch.cuda.Stream(device=dev)
-            self._frame_rgb = self.tensors()[0]
+        self._cur ^= 1
+        frame_rgb = self.tensors()[0] if self.owner else None
         for (r0, r1) in self.band_rows(bands):
             scene.render_device_band(self.width, self.height, seed, flags | _abi.RTX_FLAG_SHARD_IN_PLACE,
                                      (self.rank, self.world), r0, r1 - r0, self.rgb_ptr, self.ids_ptr,
@@ -209,21 +240,21 @@ class PeerFrame:
                 ev.record(cur)
                 self._copy_stream.wait_event(ev)
                 with torch.cuda.stream(self._copy_stream):
-                    host_rgb[y0:y1].copy_(self._frame_rgb[y0:y1], non_blocking=True)
+                    host_rgb[y0:y1].copy_(frame_rgb[y0:y1], non_blocking=True)
         if self.owner:
             cur.wait_stream(self._copy_stream)
 
     def close(self):
         lib = _abi.load()
-        if self.ptr:
+        if self.base:
             torch.cuda.synchronize(self.device)
             if self.world > 1:
                 dist.barrier(group=self.group)
             if self.owner:
-                _abi.check(lib.rtx_peer_free(self.device, C.c_void_p(self.ptr)))
+                _abi.check(lib.rtx_peer_free(self.device, C.c_void_p(self.base)))
             else:
-                _abi.check(lib.rtx_peer_close(self.device, C.c_void_p(self.ptr)))
-            self.ptr = 0
+                _abi.check(lib.rtx_peer_close(self.device, C.c_void_p(self.base)))
+            self.base = 0
 
 
 def render_distributed_p2p(scene, width, height, seed, group=None, flags=RTX_ACCEL_AUTO, want_ids=True, frame=None):

@@ -31,11 +31,22 @@ def _worker(rank, world, port, w, h, q):
         rgb2, ids2, counters2, frame = rdist.render_distributed_p2p(sc, w, h, seed=3)
         total2 = counters2.clone()
         dist.all_reduce(total2)
-        # and once more handed over to pinned host memory band by band (PeerFrame.render_to_host)
-        pin = torch.full((h, w, 3), -1.0, dtype=torch.float64).pin_memory() if rank == 0 else None
-        frame.render_to_host(sc, 3, pin, bands=3)
+        if rank == 0:  # views of the frame: keep copies, the frame is poisoned and reused below
+            rgb2, ids2 = rgb2.clone(), ids2.clone()
+        # and handed over to pinned host memory band by band (PeerFrame.render_to_host): other seeds, so that a stale
+        # or missed band cannot compare equal, into a poisoned frame and a poisoned host buffer; two frames back to
+        # back without a host synchronisation in between (the second must not tear the first one's copy-out)
+        pin = [torch.full((h, w, 3), -1.0, dtype=torch.float64).pin_memory() if rank == 0 else None for _ in range(2)]
+        frame.poison()
+        frame.render_to_host(sc, 11, pin[0], bands=3)
+        frame.render_to_host(sc, 12, pin[1], bands=2)
+        torch.cuda.synchronize()
+        # a device-resident frame again after the host frames: double buffering keeps it apart from the copies
+        frame.poison()
+        frame.render(sc, 13)
         torch.cuda.synchronize()
         if rank == 0:
+            rgb4 = frame.tensors()[0].cpu().numpy()
             full, ids_full = sc.render(w, h, seed=3, want_ids=True)
             ok = rgb.cpu().numpy().tobytes() == full.tobytes()
             ok = ok and np.array_equal(ids.cpu().numpy().view(np.uint32), ids_full)
@@ -43,7 +54,9 @@ def _worker(rank, world, port, w, h, q):
             ok2 = rgb2.cpu().numpy().tobytes() == full.tobytes()
             ok2 = ok2 and np.array_equal(ids2.cpu().numpy().view(np.uint32), ids_full)
             ok2 = ok2 and int(total2[0].item()) == sc.last_stats.rays
-            ok3 = pin.numpy().tobytes() == full.tobytes()
+            ok3 = pin[0].numpy().tobytes() == sc.render(w, h, seed=11).tobytes()
+            ok3 = ok3 and pin[1].numpy().tobytes() == sc.render(w, h, seed=12).tobytes()
+            ok3 = ok3 and rgb4.tobytes() == sc.render(w, h, seed=13).tobytes()
             q.put((bool(ok), bool(ok2), bool(ok3)))
         dist.barrier()
         frame.close()

@@ -378,3 +378,42 @@ def test_device_bands_compose_the_frame(rtx, gpu):
     sc.render_device_band(w, h, 9, rtx.RTX_ACCEL_AUTO, None, 2, 3, c.data_ptr(), None, None, st)
     torch.cuda.synchronize()
     assert bool((c[:32] == -7.0).all()) and bool((c[80:] == -7.0).all()) and bool((c[32:80] != -7.0).all())
+
+
+def test_two_renders_of_one_scene_on_two_streams(rtx, oracle, gpu):
+    """Scene::render is `&self` (scene.rs:144): renders of one scene may be issued concurrently.  The scene owns device
+    scratch (sample-queue slots, work counters), so the library orders such renders on the device with an event;
+    both frames must equal the oracle's, whichever stream or thread issued them."""
+    import threading
+    import torch
+    from rtx_b200 import scenes
+    dev = torch.device("cuda", gpu)
+    w, h = 640, 360
+    sc = scenes.sphere_demo(rays_per_pixel=8, max_bounces=6)
+    streams = [torch.cuda.Stream(device=dev) for _ in range(2)]
+    out = [torch.full((h, w, 3), float("nan"), dtype=torch.float64, device=dev) for _ in range(4)]
+    torch.cuda.synchronize(dev)
+    # one thread, two streams, four frames back to back without a host synchronisation
+    for i in range(4):
+        sc.render_device(w, h, 20 + i, rtx.RTX_FLAG_SAMPLE_QUEUE, None, out[i].data_ptr(), None, None,
+                         streams[i & 1].cuda_stream)
+    torch.cuda.synchronize(dev)
+    refs = [oracle.render_scene(sc, w, h, seed=20 + i)["rgb"] for i in range(4)]
+    for i in range(4):
+        assert float(np.abs(out[i].cpu().numpy() - refs[i]).max()) <= 1e-4, f"frame {i} (stream {i & 1})"
+    first = [o.cpu().numpy().copy() for o in out]
+    # two threads, a stream each
+    for o in out:
+        o.fill_(float("nan"))
+    torch.cuda.synchronize(dev)
+
+    def work(t):
+        for i in (t, t + 2):
+            sc.render_device(w, h, 20 + i, rtx.RTX_FLAG_SAMPLE_QUEUE, None, out[i].data_ptr(), None, None,
+                             streams[t].cuda_stream)
+    th = [threading.Thread(target=work, args=(t,)) for t in range(2)]
+    [t.start() for t in th]
+    [t.join() for t in th]
+    torch.cuda.synchronize(dev)
+    for i in range(4):
+        assert out[i].cpu().numpy().tobytes() == first[i].tobytes(), f"threaded frame {i}"
