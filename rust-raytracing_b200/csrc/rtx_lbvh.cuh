@@ -1,4 +1,5 @@
-// rtx_lbvh.cuh — LBVH node layout and the stackless traversal (K5).
+// rtx_lbvh.cuh — LBVH node layout and the traversal (K5): near-first, with a per-thread stack (not stackless: the
+// escape-pointer walk of the first build visited far more nodes; see DESIGN.md §6 for what was measured).
 //
 // The reference has no acceleration structure: closest_object is an O(N) scan (raytracing/scene.rs:243-251).
 // The LBVH must return EXACTLY what that scan returns: the same distance bits and, among equal distances,
