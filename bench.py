@@ -219,6 +219,33 @@ def timed_frames(scene, w, h, flags, steps, warmup, dev, ids_only=False, seed=1)
                 prims_per_ray=c[5] / max(c[0], 1), launches_per_frame=scene.last_device_launches)
 
 
+def graph_replay_us(scene, w, h, dev, frames=64, replays=20):
+    """The launch-bound end of C5 without the host in the loop: `frames` hit-id renders captured once into a CUDA graph
+    (every rtx_scene_render_device call is one kernel node — the work queue resets itself in the kernel) and replayed;
+    device-timed microseconds per frame."""
+    import torch
+    import rtx_b200
+    ids = torch.empty((h, w), dtype=torch.int32, device=dev)
+    side = torch.cuda.Stream(device=dev)
+    fl = rtx_b200.RTX_ACCEL_AUTO | rtx_b200.RTX_FLAG_NO_RADIANCE
+    scene.render_device(w, h, 1, fl, None, None, ids.data_ptr(), None, side.cuda_stream)  # resident before capture
+    torch.cuda.synchronize(dev)
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(g, stream=side):
+        for _ in range(frames):
+            scene.render_device(w, h, 1, fl, None, None, ids.data_ptr(), None, side.cuda_stream)
+    g.replay()
+    torch.cuda.synchronize(dev)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    st = torch.cuda.current_stream(dev)
+    e0.record(st)
+    for _ in range(replays):
+        g.replay()
+    e1.record(st)
+    torch.cuda.synchronize(dev)
+    return e0.elapsed_time(e1) * 1e3 / (frames * replays)
+
+
 def other_configs(world, rank, dev, local_rank, hbm_peak, nf_tf):
     """BASELINE.json configs[2..4], measured after the headline and outside its timed region.  N = 1: C3, C4 and the
     two ends of the C5 sweep on this GPU.  N > 1: C3 over the N ranks (PeerFrame, as the headline)."""
@@ -253,6 +280,8 @@ def other_configs(world, rank, dev, local_rank, hbm_peak, nf_tf):
         for name, (w, h) in (("C5_256x256", (256, 256)), ("C5_7680x4320", (7680, 4320))):
             r = timed_frames(sc, w, h, rtx_b200.RTX_ACCEL_AUTO, 30, 5, dev, ids_only=True)
             # per ray: 131 FP64 flops of the 7-object scan + a 4-byte id written
+            if w == 256:
+                r["us_per_frame_graph_replay"] = graph_replay_us(sc, w, h, dev)
             r.update(workload=f"C5: S1 primary-only hit ids, {w}x{h}, 1 spp", n_gpus=1, us_per_frame=r["ms_per_frame"] * 1e3,
                      roofline={"bound": "fp64", "achieved": r["mrays_s"] * 1e6 * 131 / 1e12, "peak": nf_tf, "unit": "TFLOP/s",
                                "frac": (r["mrays_s"] * 1e6 * 131 / 1e12 / nf_tf) if nf_tf else None})

@@ -60,7 +60,13 @@ enum {
   RTX_ERR_CUDA              = 2,  /* no device / CUDA runtime error (message in rtx_last_error)     */
   RTX_ERR_OUT_OF_MEMORY     = 3,
   RTX_ERR_UNSUPPORTED_SHAPE = 4,  /* user-defined CustomShape (object.rs:53-76) cannot cross the ABI */
-  RTX_ERR_INTERNAL          = 5
+  RTX_ERR_INTERNAL          = 5,
+  RTX_ERR_REFERENCE_PANIC   = 6   /* rtx_scene_render / rtx_scene_render_to_rgb8: some ray met a triangle for which the
+                                     reference's assert_eq! (object/triangle.rs:76-94) fails — there the row thread
+                                     panics and Scene::render aborts through join().unwrap() (scene.rs:167-169).  The
+                                     outputs and statistics ARE complete (such hits count as misses;
+                                     rtx_stats.triangle_panics says how many), but the reference would have produced
+                                     no image.  The device-buffer entry points report the count in d_out_counters[2] */
 };
 
 /* ---- render flags -------------------------------------------------------------------------- */
@@ -257,6 +263,21 @@ rtx_status rtx_peer_close(int32_t device, void* d_ptr);
  * `as u8`, no gamma.  out: uint8[height][width][3] (HOST), row 0 = top of the picture.             */
 rtx_status rtx_scene_render_to_rgb8(rtx_scene* scene, uint32_t width, uint32_t height, uint64_t seed, uint32_t flags,
                                     uint8_t* out_rgb8, rtx_stats* out_stats);
+/* ---- the f32 "preview" mode: the arithmetic of the reference's wgpu backend ----------------------------------
+ * ≙ gpu::Scene::render (raytracing/gpu/scene.rs:26-52) → GpuState::render (gpu/gpu_state.rs:78-107) → the fragment
+ * shader raytracing/gpu/base_shader.wgsl:64-279 with the shape snippets of object/sphere.rs:50-86, plane.rs:48-85,
+ * triangle.rs:138-194.  Same scene handle, other semantics: f32 throughout, PCG-hash RNG seeded from the pixel (no
+ * `seed`), max_bounces segments (not + 1), AABB pre-test, Moeller-Trumbore triangles, raw plane normals.  The scene,
+ * camera and config are narrowed to f32 as GpuSerialize does (`as f32`).  Running the shader itself needs wgpu, which
+ * is unavailable on this box; this is its arithmetic as a CUDA kernel (csrc/rtx_preview.cu), bit-exact against
+ * oracle/wgsl_oracle.cpp.  out_rgb: float[height][width][3], row 0 = bottom, linear (what fs_main returns, before the
+ * surface format); out_first_hit_id: uint32[height][width] object index hit by sample 0's first ray (0xFFFFFFFF =
+ * miss) or NULL.  The host variant blocks; the device variant is asynchronous on `cuda_stream`
+ * (d_out_counters: uint64[8], [0] += closest_object calls, or NULL).                                         */
+rtx_status rtx_scene_render_preview_f32(rtx_scene* scene, uint32_t width, uint32_t height, float* out_rgb,
+                                        uint32_t* out_first_hit_id, rtx_stats* out_stats);
+rtx_status rtx_scene_render_preview_f32_device(rtx_scene* scene, uint32_t width, uint32_t height, void* d_out_rgb,
+                                               void* d_out_first_hit_id, void* d_out_counters, void* cuda_stream);
 /* Device-side quantiser used by the call above (d_rgb: full-image doubles → d_out: uint8 image). */
 rtx_status rtx_quantize_rgb8_device(const void* d_rgb, uint32_t width, uint32_t height, void* d_out_rgb8, void* cuda_stream);
 

@@ -34,11 +34,69 @@ OBJECT_DTYPE = np.dtype([("type", np.int32), ("pad", np.int32), ("shape", np.flo
 _lib = None
 
 
+WGSL_LIB_PATH = os.path.join(_HERE, "libwgsl_oracle.so")
+_wgsl = None
+WGSL_OBJECT_DTYPE = np.dtype([("base", "<f4", 3), ("roughness", "<f4"), ("emission", "<f4", 3), ("type", "<u4"),
+                              ("shape", "<f4", 9)])
+
+
 def build(force=False):
-    if force or not os.path.exists(LIB_PATH) or os.path.getmtime(LIB_PATH) < os.path.getmtime(
-            os.path.join(_HERE, "rtx_oracle.cpp")):
-        subprocess.check_call(["make", "-C", _HERE, "-s", "-B", "liboracle.so"])
+    for lib, src in ((LIB_PATH, "rtx_oracle.cpp"), (WGSL_LIB_PATH, "wgsl_oracle.cpp")):
+        if force or not os.path.exists(lib) or os.path.getmtime(lib) < os.path.getmtime(os.path.join(_HERE, src)):
+            subprocess.check_call(["make", "-C", _HERE, "-s", "-B", os.path.basename(lib)])
     return LIB_PATH
+
+
+def load_wgsl():
+    """The f32 restatement of the wgpu backend's shader arithmetic (wgsl_oracle.cpp)."""
+    global _wgsl
+    if _wgsl is None:
+        build()
+        lib = C.CDLL(WGSL_LIB_PATH)
+        lib.wgsl_render.restype = C.c_int
+        lib.wgsl_render.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64, C.c_uint32, C.c_uint32,
+                                    C.c_int32, C.c_void_p, C.c_void_p, C.POINTER(C.c_uint64)]
+        lib.wgsl_rng_probe.argtypes = [C.c_float, C.c_float, C.c_uint32, C.POINTER(C.c_uint32), C.c_void_p, C.c_void_p]
+        lib.wgsl_sizeof_object.restype = C.c_uint64
+        assert lib.wgsl_sizeof_object() == WGSL_OBJECT_DTYPE.itemsize
+        _wgsl = lib
+    return _wgsl
+
+
+def wgsl_rng_probe(ux, uy, n):
+    """(seed, random_int draws uint32[n], random_float draws float32[n]) of the pixel whose uv is (ux, uy)."""
+    lib = load_wgsl()
+    seed = C.c_uint32()
+    u = np.empty(n, dtype=np.uint32)
+    f = np.empty(n, dtype=np.float32)
+    lib.wgsl_rng_probe(float(ux), float(uy), n, C.byref(seed), u.ctypes.data, f.ctypes.data)
+    return seed.value, u, f
+
+
+def render_preview_scene(scene, width, height, nthreads=0):
+    """wgsl_oracle render of an rtx_b200.Scene narrowed to f32 as GpuSerialize does (`as f32`): dict(rgb float32
+    [h][w][3] row 0 = bottom, ids uint32 [h][w], rays)."""
+    lib = load_wgsl()
+    types, shapes, mats = scene.objects_flat()
+    objs = np.zeros(len(types), dtype=WGSL_OBJECT_DTYPE)
+    with np.errstate(over="ignore"):
+        objs["type"] = types
+        objs["shape"] = shapes.astype(np.float32)
+        objs["base"] = mats[:, 0:3].astype(np.float32)
+        objs["emission"] = mats[:, 3:6].astype(np.float32)
+        objs["roughness"] = mats[:, 6].astype(np.float32)
+        cam = scene.camera
+        camv = np.array([*cam.position, *cam.get_direction(), cam.fov], dtype=np.float64).astype(np.float32)
+        c = scene.config
+        cfg_f = np.array([c.focal_length, c.focal_offset, c.non_focal_offset], dtype=np.float64).astype(np.float32)
+    cfg_u = np.array([c.rays_per_pixel, c.max_bounces], dtype=np.uint32)
+    rgb = np.empty((height, width, 3), dtype=np.float32)
+    ids = np.empty((height, width), dtype=np.uint32)
+    rays = C.c_uint64()
+    rc = lib.wgsl_render(camv.ctypes.data, cfg_u.ctypes.data, cfg_f.ctypes.data, objs.ctypes.data if len(objs) else None,
+                         len(objs), width, height, nthreads, rgb.ctypes.data, ids.ctypes.data, C.byref(rays))
+    assert rc == 0
+    return dict(rgb=rgb, ids=ids, rays=rays.value)
 
 
 def load():

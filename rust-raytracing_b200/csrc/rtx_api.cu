@@ -270,8 +270,11 @@ uint32_t choose_accel(const rtx_scene* s, uint32_t flags) {
 // The device-side alias of a host pointer when the allocation is pinned and mapped (zero-copy), else null.
 template <typename T>
 static T* mapped_device_pointer(T* host) {
+#ifdef RTX_MEASUREMENT_KNOBS  // measurement builds only: a stray environment variable must not change the product's path
   static const bool enabled = [] { const char* v = getenv("RTX_ZERO_COPY"); return !v || atoi(v) != 0; }();
-  if (!enabled || !host) return nullptr;
+  if (!enabled) return nullptr;
+#endif
+  if (!host) return nullptr;
   cudaPointerAttributes a{};
   if (cudaPointerGetAttributes(&a, host) != cudaSuccess) {
     cudaGetLastError();
@@ -343,7 +346,7 @@ static rtx_status render_common_on_stream(rtx_scene* s, uint32_t width, uint32_t
     shard_band_tiles(width, height, sh.index, sh.count, tile_rows[0], tile_rows[1], &p.tile_first, &p.my_tiles);
   }
   if (p.my_tiles == 0) return RTX_OK;
-  p.tail_first = p.my_tiles * GRANS_PER_TILE, p.tail_granules = 0, p.tail_scratch = nullptr, p.tail_done = nullptr;
+  p.tail_first = p.my_tiles * GRANS_PER_TILE, p.tail_granules = 0, p.tail_scratch = nullptr;
   const bool pool = !p.lane_kernel && pool_kernel_eligible(p);
   // A large frame bound for pinned host memory: bands of tile rows, each rendered with the sample queue into the
   // scene's device frame and copied out by the copy engine while the next band renders (C2 e2e 12.2 -> 11.5 ms
@@ -404,6 +407,13 @@ static rtx_status render_common(rtx_scene* s, uint32_t width, uint32_t height, u
                                 const rtx_shard* shard, double* d_rgb, uint32_t* d_ids, unsigned long long* d_counters,
                                 uint32_t* d_work_counter, cudaStream_t stream, uint32_t* launches, double* host_rgb = nullptr,
                                 const uint32_t* tile_rows = nullptr) {
+  // A stream under CUDA graph capture takes no part in this: an event recorded into a capture cannot be waited for
+  // outside it.  The caller who captures renders orders them against its other work itself.
+  cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
+  if (cudaStreamIsCapturing(stream, &cap) != cudaSuccess) cudaGetLastError(), cap = cudaStreamCaptureStatusNone;
+  if (cap != cudaStreamCaptureStatusNone)
+    return render_common_on_stream(s, width, height, seed, flags, shard, d_rgb, d_ids, d_counters, d_work_counter, stream,
+                                   launches, host_rgb, tile_rows);
   if (!s->ev_last) RTX_CUDA_TRY(s, cudaEventCreateWithFlags(&s->ev_last, cudaEventDisableTiming));
   if (s->last_valid && s->last_stream != stream) RTX_CUDA_TRY(s, cudaStreamWaitEvent(stream, s->ev_last, 0));
   const rtx_status st = render_common_on_stream(s, width, height, seed, flags, shard, d_rgb, d_ids, d_counters, d_work_counter,
@@ -555,7 +565,9 @@ rtx_status rtx_scene_create(const rtx_camera* camera, const rtx_config* config, 
   if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking);
   if (e == cudaSuccess) e = cudaEventCreate(&s->ev0);
   if (e == cudaSuccess) e = cudaEventCreate(&s->ev1);
-  if (e == cudaSuccess) e = cudaMalloc((void**)&s->d_work_counter, 64 * sizeof(uint32_t));
+  // 64 work queues of {next entry, CTAs out}: zero here, and every render kernel leaves its queue zero (queue_release)
+  if (e == cudaSuccess) e = cudaMalloc((void**)&s->d_work_counter, 64 * 2 * sizeof(uint32_t));
+  if (e == cudaSuccess) e = cudaMemset(s->d_work_counter, 0, 64 * 2 * sizeof(uint32_t));
   if (e == cudaSuccess) e = cudaMalloc((void**)&s->d_counters, 8 * sizeof(unsigned long long));
   if (e != cudaSuccess) {
     rtx_status st = cuda_fail(nullptr, e, "rtx_scene_create");
@@ -581,6 +593,7 @@ rtx_status rtx_scene_destroy(rtx_scene* s) {
   cudaFree(s->d_rgb);
   cudaFree(s->d_ids);
   cudaFree(s->d_rgb8);
+  cudaFree(s->d_pv);
   if (s->ev0) cudaEventDestroy(s->ev0);
   if (s->ev1) cudaEventDestroy(s->ev1);
   if (s->ev_last) cudaEventDestroy(s->ev_last);
@@ -638,11 +651,13 @@ rtx_status rtx_scene_add_spheres(rtx_scene* s, const rtx_sphere* shapes, const r
     const size_t o = s->sph.size();
     s->sph.resize(o + SPH_STRIDE);
     pack_sphere(&shapes[i].position.x, shapes[i].radius, &s->sph[o]);
+    s->sph_radius.push_back(shapes[i].radius);
     s->obj_ref.push_back(REF_SPHERE | (uint32_t)s->sph_id.size());
     s->sph_id.push_back((uint32_t)s->n_obj++);
     push_material(s, materials[i]);
   }
   s->dirty = true;
+  s->pv_valid = false;
   s->bvh_valid = false;
   return RTX_OK;
 }
@@ -660,6 +675,7 @@ rtx_status rtx_scene_add_planes(rtx_scene* s, const rtx_plane* shapes, const rtx
     push_material(s, materials[i]);
   }
   s->dirty = true;
+  s->pv_valid = false;
   s->bvh_valid = false;
   return RTX_OK;
 }
@@ -679,6 +695,7 @@ rtx_status rtx_scene_add_triangles(rtx_scene* s, const rtx_triangle* shapes, con
     push_material(s, materials[i]);
   }
   s->dirty = true;
+  s->pv_valid = false;
   s->bvh_valid = false;
   return RTX_OK;
 }
@@ -706,10 +723,12 @@ rtx_status rtx_scene_update_spheres(rtx_scene* s, const uint64_t* idx, const rtx
   for (uint64_t i = 0; i < n; ++i) {
     const uint32_t k = s->obj_ref[idx[i]] & REF_INDEX_MASK;
     pack_sphere(&shapes[i].position.x, shapes[i].radius, &s->sph[(size_t)k * SPH_STRIDE]);
+    s->sph_radius[k] = shapes[i].radius;
     s->upd_sph.push_back(k);
     if (materials) update_material(s, idx[i], materials[i]);
   }
   if (n) s->bvh_refit = true;
+  s->pv_valid = false;
   return RTX_OK;
 }
 rtx_status rtx_scene_update_planes(rtx_scene* s, const uint64_t* idx, const rtx_plane* shapes, const rtx_material* materials,
@@ -724,6 +743,7 @@ rtx_status rtx_scene_update_planes(rtx_scene* s, const uint64_t* idx, const rtx_
     s->upd_pl.push_back(k);
     if (materials) update_material(s, idx[i], materials[i]);
   }
+  s->pv_valid = false;
   return RTX_OK;
 }
 rtx_status rtx_scene_update_triangles(rtx_scene* s, const uint64_t* idx, const rtx_triangle* shapes,
@@ -746,6 +766,7 @@ rtx_status rtx_scene_update_triangles(rtx_scene* s, const uint64_t* idx, const r
     if (materials) update_material(s, idx[i], materials[i]);
   }
   if (n) s->bvh_refit = true;
+  s->pv_valid = false;
   return RTX_OK;
 }
 rtx_status rtx_scene_rebuild_accel(rtx_scene* s) {
@@ -762,11 +783,12 @@ uint32_t rtx_scene_last_launches(const rtx_scene* s) { return s ? s->last_launch
 rtx_status rtx_scene_clear_objects(rtx_scene* s) {
   if (!s) return fail(s, RTX_ERR_INVALID_ARGUMENT, "null scene");
   std::lock_guard<std::mutex> lk(s->mu);
-  s->sph.clear(), s->pl.clear(), s->tri.clear(), s->mat.clear(), s->tri_raw.clear();
+  s->sph.clear(), s->pl.clear(), s->tri.clear(), s->mat.clear(), s->tri_raw.clear(), s->sph_radius.clear();
   s->sph_id.clear(), s->pl_id.clear(), s->tri_id.clear(), s->obj_ref.clear();
   s->upd_sph.clear(), s->upd_pl.clear(), s->upd_tri.clear(), s->upd_mat.clear();
   s->n_obj = 0;
   s->dirty = true;
+  s->pv_valid = false;
   s->bvh_valid = false;
   return RTX_OK;
 }
@@ -793,7 +815,7 @@ rtx_status rtx_scene_render_device(rtx_scene* s, uint32_t width, uint32_t height
     return fail(s, RTX_ERR_INVALID_ARGUMENT, "no output buffer");
   std::lock_guard<std::mutex> lk(s->mu);
   RTX_CUDA_TRY(s, cudaSetDevice(s->device));
-  uint32_t* wc = s->d_work_counter + (s->wc_slot++ & 63u);  // under s->mu
+  uint32_t* wc = s->d_work_counter + 2u * (s->wc_slot++ & 63u);  // under s->mu
   uint32_t launches = 0;
   const rtx_status st = render_common(s, width, height, seed, flags, shard, (double*)d_out_rgb, (uint32_t*)d_out_primary_hit_id,
                                       (unsigned long long*)d_out_counters, wc, (cudaStream_t)cuda_stream, &launches);
@@ -810,7 +832,7 @@ rtx_status rtx_scene_render_device_band(rtx_scene* s, uint32_t width, uint32_t h
     return fail(s, RTX_ERR_INVALID_ARGUMENT, "no output buffer");
   std::lock_guard<std::mutex> lk(s->mu);
   RTX_CUDA_TRY(s, cudaSetDevice(s->device));
-  uint32_t* wc = s->d_work_counter + (s->wc_slot++ & 63u);  // under s->mu
+  uint32_t* wc = s->d_work_counter + 2u * (s->wc_slot++ & 63u);  // under s->mu
   uint32_t launches = 0;
   const uint32_t rows[2] = {tile_row_first, tile_row_count};
   const rtx_status st = render_common(s, width, height, seed, flags, shard, (double*)d_out_rgb, (uint32_t*)d_out_primary_hit_id,
@@ -879,6 +901,10 @@ rtx_status rtx_scene_render(rtx_scene* s, uint32_t width, uint32_t height, uint6
     out_stats->total_ms =
         std::chrono::duration<float, std::milli>(std::chrono::steady_clock::now() - t0).count();
   }
+  if (counters[2] != 0)
+    return fail(s, RTX_ERR_REFERENCE_PANIC,
+                std::to_string(counters[2]) + " ray/triangle tests hit an assert_eq! of the reference (triangle.rs:76-94): "
+                "the reference's render would have panicked; the outputs hold the image with those hits rejected");
   return RTX_OK;
 }
 
@@ -954,6 +980,10 @@ rtx_status rtx_scene_render_to_rgb8(rtx_scene* s, uint32_t width, uint32_t heigh
     out_stats->total_ms =
         std::chrono::duration<float, std::milli>(std::chrono::steady_clock::now() - t0).count();
   }
+  if (counters[2] != 0)
+    return fail(s, RTX_ERR_REFERENCE_PANIC,
+                std::to_string(counters[2]) + " ray/triangle tests hit an assert_eq! of the reference (triangle.rs:76-94): "
+                "the reference's render would have panicked; the outputs hold the image with those hits rejected");
   return RTX_OK;
 }
 

@@ -23,6 +23,7 @@ struct rtx_scene {
   std::vector<uint32_t> sph_id, pl_id, tri_id;
   std::vector<float> sph32;     // f32 copy of `sph` for the scan's conservative cull (rebuilt at upload)
   std::vector<double> tri_raw;  // 9 doubles per triangle: the LBVH builder needs the vertices for boxes
+  std::vector<double> sph_radius;  // per sphere: the radius as given (`sph` keeps radius*radius); the f32 preview needs it
   std::vector<uint32_t> obj_ref;  // per object: REF_* | index within its shape array
   uint64_t n_obj = 0;
   bool dirty = true;              // layout changed: rebuild and upload the whole blob
@@ -74,6 +75,12 @@ struct rtx_scene {
   size_t d_ids_cap = 0;
   uint8_t* d_rgb8 = nullptr;
   size_t d_rgb8_cap = 0;
+
+  // f32 preview (rtx_preview.cu): nine float4 arrays of the object list; pv_valid drops whenever an object changes
+  float* d_pv = nullptr;
+  size_t d_pv_cap = 0;
+  uint32_t pv_stride = 0, pv_bytes = 0;
+  bool pv_valid = false;
 
   cudaStream_t stream = nullptr;  // used by the blocking host-buffer entry points
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;

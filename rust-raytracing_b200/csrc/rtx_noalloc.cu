@@ -105,7 +105,8 @@ extern "C" rtx_status rtx_scene_render_device_noalloc(rtx_scene* s, uint32_t wid
   p.out_ids = static_cast<uint32_t*>(d_out_primary_hit_id);
   if (!pool_kernel_eligible(p))
     return fail(s, RTX_ERR_INVALID_ARGUMENT,
-                "rtx_scene_render_device_noalloc: the scene does not fit the shared-memory scan kernel (packed scene > 16 KB)");
+                "rtx_scene_render_device_noalloc: only the context-pool kernel uses scratch — it takes scanned scenes whose "
+                "packed size is <= 16 KB, rendered with max_bounces >= 1");
   const size_t need = pool_plan_tail(p, s->sm_count);
   if (need == 0)
     return fail(s, RTX_ERR_INVALID_ARGUMENT,
@@ -118,7 +119,9 @@ extern "C" rtx_status rtx_scene_render_device_noalloc(rtx_scene* s, uint32_t wid
                     "; use rtx_scene_render_device or render fewer pixels / samples per call");
   p.tail_scratch = reinterpret_cast<double*>(scratch + NOALLOC_COUNTER_BYTES);
   uint32_t launches = 0;
-  // clears the work counter on `cuda_stream`, launches render_pool_kernel + tail_sum_kernel: no allocation
+  // the work queue's two words must start at zero (a launch leaves them zero, but the array is shared with every other
+  // caller on this GPU: clear them); then render_pool_kernel + tail_sum_kernel: no allocation
+  RTX_CUDA_TRY(s, cudaMemsetAsync(scratch, 0, 2 * sizeof(uint32_t), (cudaStream_t)cuda_stream));
   const cudaError_t e = launch_render_pool(p, s->sm_count, (cudaStream_t)cuda_stream, &launches);
   if (e != cudaSuccess) return cuda_fail(s, e, "rtx_scene_render_device_noalloc launch");
   s->last_launches = launches;

@@ -220,6 +220,7 @@ __global__ void __launch_bounds__(RENDER_BLOCK, USE_BVH ? BVH_BLOCKS_PER_SM : 2)
       atomicAdd(&p.ray_counter[5], pt);
     }
   }
+  queue_release(p);
 }
 
 // Launch helper used by the API layer.  Returns the cudaError of the launch.
@@ -228,8 +229,7 @@ cudaError_t launch_render(const RenderParams& p, int sm_count, cudaStream_t stre
   constexpr uint32_t SMEM_LIMIT = 64u * 1024u;
   const bool use_smem = p.layout.bytes > 0 && p.layout.bytes <= SMEM_LIMIT;
   const size_t smem = use_smem ? (size_t)p.layout.bytes + 128 : 0;
-  cudaError_t e = cudaMemsetAsync(p.work_counter, 0, sizeof(uint32_t), stream);
-  if (e != cudaSuccess) return e;
+  cudaError_t e = cudaSuccess;
   const int blocks_per_sm = p.use_bvh ? BVH_BLOCKS_PER_SM : 2;
   const uint64_t total_work = (uint64_t)p.my_tiles * GRANS_PER_TILE;
   // persistent grid: a multiple of the SM count, never more warps than granules

@@ -40,7 +40,10 @@ struct RenderParams {
   uint32_t my_tiles;    // tiles of this shard this launch renders ...
   uint32_t tile_first;  // ... starting at this one (a band of the shard's tile list; 0 = from the start)
   uint32_t compact;     // 1: outputs use the compact per-shard tile layout
-  uint32_t* work_counter;  // zeroed before launch
+  // The atomic work queue: [0] next entry, [1] CTAs that have left the queue.  Both are zero when a launch starts and
+  // the launch leaves them zero (queue_release: the last CTA out resets them) — no memset between frames, which in
+  // the launch-bound regime (C5 at 256x256) was one of the three stream operations of a frame.
+  uint32_t* work_counter;
   // outputs
   double* out_rgb;                  // may be null (RTX_FLAG_NO_RADIANCE)
   uint32_t* out_ids;                // may be null
@@ -51,7 +54,6 @@ struct RenderParams {
   // tail_sum_kernel adds up per pixel in sample order (the reference's left fold).
   uint32_t tail_first, tail_granules;
   double* tail_scratch;
-  uint32_t* tail_done;  // unused
   unsigned long long* ray_counter;  // [0] rays, [1] paths, [2] triangle panics, [3] hits, [4] nodes visited, [5] prims tested; may be null
 };
 
@@ -88,6 +90,18 @@ __device__ __forceinline__ void granule_pixel(const RenderParams& p, const Granu
     *y = g.y0 + k / g.w;
   }
   *out_index = p.compact ? g.base_out + (*y - g.ty0) * TILE + (*x - g.tx0) : *y * p.width + *x;
+}
+
+// Last thing a render kernel does (every thread of the CTA must get here): the last CTA out zeroes the queue.
+__device__ __forceinline__ void queue_release(const RenderParams& p) {
+  __syncthreads();  // every warp of this CTA has seen the queue run dry: no more atomics on [0] from here
+  if (threadIdx.x == 0) {
+    __threadfence();
+    if (atomicAdd(p.work_counter + 1, 1u) + 1u == gridDim.x) {
+      p.work_counter[0] = 0u;
+      p.work_counter[1] = 0u;
+    }
+  }
 }
 
 // ---- TMA bulk copy (global → shared) with an mbarrier ------------------------------------------

@@ -125,7 +125,9 @@ __global__ void __launch_bounds__(POOL_WARPS * 32, MIN_BLOCKS) __maxnreg__(pool_
   P.w = reinterpret_cast<unsigned long long*>(smem_raw + pools_off + warp * POOL_BYTES_PER_WARP);
   unsigned char* idx = smem_raw + pools_off + POOL_WARPS * POOL_BYTES_PER_WARP + warp * POOL_WARP_SCRATCH;
   double* sctab = reinterpret_cast<double*>(smem_raw + pools_off + POOL_WARPS * POOL_BYTES_PER_WARP + POOL_WARPS * POOL_WARP_SCRATCH);
-  for (uint32_t i = threadIdx.x; i < 440u; i += POOL_BLOCK) sctab[i] = SINCOS_TAB_DEV[i];
+  // (a depth-0 render never bounces: nothing reads the table)
+  if (p.max_bounces != 0)
+    for (uint32_t i = threadIdx.x; i < 440u; i += POOL_BLOCK) sctab[i] = SINCOS_TAB_DEV[i];
   __syncthreads();
 
   const V3 cam_pos = mk3(p.cam_pos[0], p.cam_pos[1], p.cam_pos[2]);
@@ -386,11 +388,16 @@ __global__ void __launch_bounds__(POOL_WARPS * 32, MIN_BLOCKS) __maxnreg__(pool_
       atomicAdd(&p.ray_counter[5], pt);
     }
   }
+  queue_release(p);
 }
 
+// Scanned scenes whose blob fits next to the pools.  Not for primary-only renders (max_bounces == 0, config C5): every
+// path is one ray, there is no divergence for the pool to repair, and the lane kernel's shorter prologue and loop win
+// at every size (CUDA-graph replay, tools/bench_c5_small.py: 256x256 7.2 vs 12.7 us per frame, 7680x4320 1.309 vs
+// 1.362 ms).
 bool pool_kernel_eligible(const RenderParams& p) {
   return !p.use_bvh && p.layout.bytes > 0 && p.layout.bytes <= 16u * 1024u && p.rays_per_pixel < 0x7FFFFFFFull &&
-         p.max_bounces < 0x7FFFFFFEull;
+         p.max_bounces != 0 && p.max_bounces < 0x7FFFFFFEull;
 }
 
 // Which queue this launch uses.
@@ -414,9 +421,13 @@ size_t pool_plan_tail(RenderParams& p, int sm_count) {
   p.tail_first = (uint32_t)granules;
   p.tail_granules = 0;
   p.tail_scratch = nullptr;
-  p.tail_done = nullptr;
-  // RTX_QUEUE_MODE (measurement knob, only when the caller left the choice open): 1 pixel queue, 2 sample queue
+  // RTX_QUEUE_MODE (measurement builds, -DRTX_MEASUREMENT_KNOBS, and only when the caller left the choice open):
+  // 1 pixel queue, 2 sample queue
+#ifdef RTX_MEASUREMENT_KNOBS
   static const int env_mode = [] { const char* v = getenv("RTX_QUEUE_MODE"); return v ? atoi(v) : 0; }();
+#else
+  constexpr int env_mode = 0;
+#endif
   const uint32_t mode = p.queue_mode ? p.queue_mode : (uint32_t)env_mode;
   const uint64_t rpp = p.rays_per_pixel;
   if (mode == 1 || !p.out_rgb || rpp < 1 || rpp > 65536) return 0;
@@ -435,7 +446,11 @@ size_t pool_plan_tail(RenderParams& p, int sm_count) {
 
 uint32_t pool_host_bands(const RenderParams& p, int sm_count) {
   if (p.queue_mode != 0 || !p.out_rgb || p.shard_count != 1 || p.rays_per_pixel < 4 || p.rays_per_pixel > 65536) return 1;
-  static const int env_bands = [] { const char* v = getenv("RTX_HOST_BANDS"); return v ? atoi(v) : 0; }();  // measurement knob
+#ifdef RTX_MEASUREMENT_KNOBS
+  static const int env_bands = [] { const char* v = getenv("RTX_HOST_BANDS"); return v ? atoi(v) : 0; }();
+#else
+  constexpr int env_bands = 0;
+#endif
   const uint64_t contexts = (uint64_t)sm_count * 24 * POOL_SLOTS_MAX;
   const uint64_t pixels = (uint64_t)p.width * p.height;
   // measured on C2 (9.1 pixels per context): 1 band (pixel queue, zero-copy) 12.21 ms, 2: 11.57, 3: 11.46, 4: 11.39, 6: 11.42, 8: 11.43
@@ -460,8 +475,7 @@ template <int POOL_SLOTS, int MIN_BLOCKS, bool SAMPLE_QUEUE, int POOL_WARPS = 8,
 static cudaError_t launch_pool_variant(const RenderParams& p, int sm_count, cudaStream_t stream, uint32_t* out_launches) {
   constexpr int POOL_BLOCK = POOL_WARPS * 32;
   const size_t smem = pool_smem_bytes<POOL_SLOTS, SAMPLE_QUEUE, POOL_WARPS>(p.layout.bytes);
-  cudaError_t e = cudaMemsetAsync(p.work_counter, 0, sizeof(uint32_t), stream);
-  if (e != cudaSuccess) return e;
+  cudaError_t e = cudaSuccess;
   const uint64_t total_work =
       (uint64_t)p.tail_first + (uint64_t)p.tail_granules * ((p.rays_per_pixel + SAMPLES_PER_ENTRY - 1) / SAMPLES_PER_ENTRY);
   // persistent grid: MIN_BLOCKS CTAs per SM, never more contexts than queue entries can feed
@@ -506,8 +520,12 @@ static cudaError_t launch_pool_for_scene(const RenderParams& p, int sm_count, cu
 }
 
 cudaError_t launch_render_pool(const RenderParams& p, int sm_count, cudaStream_t stream, uint32_t* out_launches) {
-  // RTX_POOL_VARIANT (measurement knob): 0 = auto; 1 = 2 CTAs x 8 warps; 2 = 1 x 20 warps; 3 = 1 x 24 warps (sample queue only)
+  // RTX_POOL_VARIANT (measurement builds only): 0 = auto; 1 = 2 CTAs x 8 warps; 2 = 1 x 20 warps; 3 = 1 x 24 warps (sample queue only)
+#ifdef RTX_MEASUREMENT_KNOBS
   static const int variant = [] { const char* v = getenv("RTX_POOL_VARIANT"); return v ? atoi(v) : 0; }();
+#else
+  constexpr int variant = 0;
+#endif
   static const size_t optin = pool_smem_optin();
   const uint32_t blob = p.layout.bytes;
   if (p.tail_granules != 0) {  // sample queue

@@ -16,6 +16,12 @@
 //
 // Range: |x| < 105414350 (0x419921FB) like glibc's fast paths; beyond that glibc runs its multi-precision
 // __branred reduction, which is not restated — callers here only pass theta in [0, 2*pi).
+//
+// Provenance and licence: the algorithm and the constants restated here, and the table in rtx_sincostab.inc, come from
+// the GNU C Library (sysdeps/ieee754/dbl-64/s_sin.c, sincostab.c; Copyright (C) Free Software Foundation, Inc.), which
+// is distributed under the GNU Lesser General Public License, version 2.1 or later.  This file and rtx_sincostab.inc
+// are therefore offered under LGPL-2.1-or-later (SPDX-License-Identifier: LGPL-2.1-or-later), whatever licence the
+// rest of this repository carries.
 #pragma once
 #include "rtx_math.cuh"
 

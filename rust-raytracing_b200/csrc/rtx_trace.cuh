@@ -2,7 +2,7 @@
 //
 // Every function is the hoisted, bit-identical form of a reference routine; the derivations (why each
 // rewrite cannot change a single output bit) are in DESIGN.md §"Exact rewrites" and are enforced by the
-// per-function parity tests (tests/test_gpu_parity.py) against the as-written CPU oracle.
+// per-function parity tests (tests/test_gpu_functions.py) against the as-written CPU oracle.
 #pragma once
 #if defined(__CUDACC__)
 #include <math_constants.h>

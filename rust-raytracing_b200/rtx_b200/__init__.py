@@ -445,6 +445,22 @@ class Scene:
         self.last_stats = st
         return img
 
+    def render_preview(self, width, height, want_ids=False):
+        """The f32 preview (the wgpu backend's arithmetic, base_shader.wgsl): float32 [height][width][3], row 0 = bottom;
+        with want_ids also the object index sample 0's first ray hits."""
+        h = self._sync()
+        rgb = np.empty((height, width, 3), dtype=np.float32)
+        ids = np.empty((height, width), dtype=np.uint32) if want_ids else None
+        st = Stats()
+        _abi.check(_abi.load().rtx_scene_render_preview_f32(h, width, height, rgb.ctypes.data,
+                                                            ids.ctypes.data if ids is not None else None, C.byref(st)), h)
+        self.last_stats = st
+        return (rgb, ids) if want_ids else rgb
+
+    def render_preview_device(self, width, height, d_rgb, d_ids, d_counters, stream):
+        h = self._sync()
+        _abi.check(_abi.load().rtx_scene_render_preview_f32_device(h, width, height, d_rgb, d_ids, d_counters, stream), h)
+
     def render_device(self, width, height, seed, flags, shard, d_rgb, d_ids, d_counters, stream):
         """Asynchronous device-buffer render (raw device pointers / cudaStream_t as ints)."""
         h = self._sync()

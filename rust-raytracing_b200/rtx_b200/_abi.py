@@ -69,6 +69,8 @@ RTX_ERR_INVALID_ARGUMENT = 1
 RTX_ERR_CUDA = 2
 RTX_ERR_OUT_OF_MEMORY = 3
 RTX_ERR_UNSUPPORTED_SHAPE = 4
+RTX_ERR_INTERNAL = 5
+RTX_ERR_REFERENCE_PANIC = 6
 RTX_ACCEL_AUTO, RTX_ACCEL_BRUTE, RTX_ACCEL_LBVH = 0, 1, 2
 RTX_FLAG_NO_RADIANCE = 4
 RTX_FLAG_LANE_KERNEL = 8
@@ -120,6 +122,8 @@ SIGNATURES = {
     "rtx_shard_tile_count": (C.c_uint64, [C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32]),
     "rtx_deinterleave_tiles": (C.c_int32, [C.c_uint32, C.c_uint32, C.c_uint32, _vp, _vp, _vp, _vp, _vp]),
     "rtx_scene_render_to_rgb8": (C.c_int32, [_vp, C.c_uint32, C.c_uint32, C.c_uint64, C.c_uint32, _vp, _P(Stats)]),
+    "rtx_scene_render_preview_f32": (C.c_int32, [_vp, C.c_uint32, C.c_uint32, _vp, _vp, _P(Stats)]),
+    "rtx_scene_render_preview_f32_device": (C.c_int32, [_vp, C.c_uint32, C.c_uint32, _vp, _vp, _vp, _vp]),
     "rtx_quantize_rgb8_device": (C.c_int32, [_vp, C.c_uint32, C.c_uint32, _vp, _vp]),
     "rtx_last_error": (C.c_char_p, [_vp]),
     "rtx_abi_version": (C.c_uint32, []),

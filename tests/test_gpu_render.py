@@ -144,7 +144,7 @@ def test_render_to_image_matches_oracle_quantiser(rtx, oracle, gpu):  # scene.rs
 
 def test_sharded_render_is_byte_identical(rtx, gpu):
     """N-shard image == 1-shard image byte for byte (one GPU plays every rank; the N-rank NCCL path is
-    covered by tests/test_dist.py)."""
+    covered by tests/test_dist_cpu.py and tests/test_dist_gpu.py)."""
     import torch
     from rtx_b200 import scenes
     from rtx_b200 import dist as rdist
@@ -417,3 +417,27 @@ def test_two_renders_of_one_scene_on_two_streams(rtx, oracle, gpu):
     torch.cuda.synchronize(dev)
     for i in range(4):
         assert out[i].cpu().numpy().tobytes() == first[i].tobytes(), f"threaded frame {i}"
+
+
+def test_reference_panic_is_reported(rtx, oracle, gpu):
+    """A triangle whose elimination trips an assert_eq! of the reference (triangle.rs:76-94; here: an infinite
+    coordinate makes lgs1.x / lgs1.x NaN) panics the reference's row thread and aborts Scene::render.  The CUDA path
+    rejects the hit, counts it, completes the image — and rtx_scene_render says so with RTX_ERR_REFERENCE_PANIC."""
+    import ctypes as C
+    from rtx_b200 import Material, Object, Triangle, scenes
+    sc = scenes.sphere_demo(rays_per_pixel=1, max_bounces=2)
+    w, h = 64, 48
+    clean = sc.render(w, h, seed=3)
+    sc.add_object(Object(Triangle([(float("inf"), 0, 0), (5, 1, 0), (5, 0, 1)]), Material.colored((1, 1, 1))))
+    with pytest.raises(rtx.RtxError) as e:
+        sc.render(w, h, seed=3)
+    assert e.value.status == rtx._abi.RTX_ERR_REFERENCE_PANIC and "assert_eq" in str(e.value)
+    # the outputs and statistics are complete all the same: through the C ABI directly
+    lib, hnd = rtx._abi.load(), sc._sync()
+    rgb = np.full((h, w, 3), np.nan)
+    st = rtx._abi.Stats()
+    status = lib.rtx_scene_render(hnd, w, h, 3, 0, rgb.ctypes.data, None, C.byref(st))
+    assert status == rtx._abi.RTX_ERR_REFERENCE_PANIC and st.triangle_panics > 0 and st.pixels == w * h
+    ref = oracle.render_scene(sc, w, h, seed=3)
+    assert ref["panics"] == st.triangle_panics
+    assert rgb.tobytes() == clean.tobytes()  # the rejected triangle changes nothing
