@@ -83,6 +83,11 @@ enum {
   RTX_FLAG_SAMPLE_QUEUE = 64u,    /* context-pool kernel: force (pixel, sample) queue entries + ordered sum
                                      pass (short tail: small images, multi-GPU shards).  Default: chosen
                                      from pixels per resident context.  Same image either way.         */
+  RTX_FLAG_SHARD_ROWS = 128u,     /* shard by full-width STRIPS of 4 pixel rows (strip s belongs to shard s % count)
+                                     instead of 16x16 tiles, written in place like RTX_FLAG_SHARD_IN_PLACE: a
+                                     shard's pixels are whole contiguous rows of the frame, which each GPU's copy
+                                     engine can deliver to a shared host frame over its own PCIe link
+                                     (rtx_scene_render_rows_to_host).  The image does not depend on ownership.  */
   RTX_FLAG_SHARD_IN_PLACE = 16u   /* with shard->count > 1: write this shard's pixels at their final
                                      position of the FULL image layout instead of a compact buffer.
                                      d_out_* may then be another GPU's memory (rtx_peer_open): every
@@ -203,6 +208,44 @@ rtx_status rtx_scene_render_device_band(rtx_scene* scene, uint32_t width, uint32
 rtx_status rtx_scene_render_device_noalloc(rtx_scene* scene, uint32_t width, uint32_t height, uint64_t seed,
                                            uint32_t flags, void* d_out_rgb, void* d_out_primary_hit_id,
                                            void* cuda_stream);
+/* Multi-GPU frames bound for HOST memory without a rank-0 funnel: every GPU delivers its own pixels to their final
+ * place in ONE host frame over its own PCIe link.  The shard is cut by rows (RTX_FLAG_SHARD_ROWS is implied),
+ * rendered in bands into the scene's own device frame, and after each band the GPU's copy engine moves the band's
+ * strips to host_rgb ([height][width][3] doubles, the WHOLE frame; pinned: rtx_host_alloc, or rtx_host_frame_* when
+ * the GPUs belong to different processes) while the next band renders.  Asynchronous on `cuda_stream`, which is done
+ * when this shard's rows are in host memory; the frame is complete when every shard's call is (≙ the join of
+ * scene.rs:167-169).  host_ids: uint32[height][width] or NULL.  d_out_counters as in rtx_scene_render_device.   */
+rtx_status rtx_scene_render_rows_to_host(rtx_scene* scene, uint32_t width, uint32_t height, uint64_t seed, uint32_t flags,
+                                         const rtx_shard* shard, double* host_rgb, uint32_t* host_ids,
+                                         void* d_out_counters, void* cuda_stream);
+/* One pinned host frame shared by the processes of a node: POSIX shared memory `name` ("/rtx-frame-...") mapped and
+ * registered with CUDA in each process.  create: exclusive, sized `bytes`; open: an existing one; close: unregister +
+ * unmap, and unlink the name when unlink_name != NULL (the creator).                                             */
+rtx_status rtx_host_frame_create(const char* name, uint64_t bytes, void** out);
+rtx_status rtx_host_frame_open(const char* name, uint64_t bytes, void** out);
+rtx_status rtx_host_frame_close(void* ptr, uint64_t bytes, const char* unlink_name);
+
+/* ---- N GPUs of one process behind one handle ---------------------------------------------------------------
+ * ≙ Scene::{new, add_object, render} (raytracing/scene.rs:112-170) for a caller that wants every GPU of the box
+ * without processes, NCCL or Python: one scene per device, one worker thread per device inside the library.
+ * rtx_multi_render blocks like Scene::render and returns the whole image in HOST memory (pinned for speed); each
+ * GPU renders its rows and delivers them itself (rtx_scene_render_rows_to_host).  The image equals the one-GPU
+ * image byte for byte.  rtx_multi_scene(i) is device i's scene handle, for the calls that have no rtx_multi_ form
+ * (updates, wire ingest) — apply them to every device's scene.                                                  */
+typedef struct rtx_multi rtx_multi;
+rtx_status rtx_multi_create(const rtx_camera* camera, const rtx_config* config, const int32_t* devices, uint32_t n_devices,
+                            rtx_multi** out);
+rtx_status rtx_multi_destroy(rtx_multi* multi);
+uint32_t   rtx_multi_device_count(const rtx_multi* multi);
+rtx_scene* rtx_multi_scene(rtx_multi* multi, uint32_t i);
+rtx_status rtx_multi_set_camera(rtx_multi* multi, const rtx_camera* camera);
+rtx_status rtx_multi_set_config(rtx_multi* multi, const rtx_config* config);
+rtx_status rtx_multi_add_spheres(rtx_multi* multi, const rtx_sphere* shapes, const rtx_material* materials, uint64_t n);
+rtx_status rtx_multi_add_planes(rtx_multi* multi, const rtx_plane* shapes, const rtx_material* materials, uint64_t n);
+rtx_status rtx_multi_add_triangles(rtx_multi* multi, const rtx_triangle* shapes, const rtx_material* materials, uint64_t n);
+rtx_status rtx_multi_clear_objects(rtx_multi* multi);
+rtx_status rtx_multi_render(rtx_multi* multi, uint32_t width, uint32_t height, uint64_t seed, uint32_t flags,
+                            double* out_rgb, uint32_t* out_primary_hit_id, rtx_stats* out_stats);
 /* Number of tiles (and therefore compact-buffer slots) shard `index` of `count` owns. */
 uint64_t   rtx_shard_tile_count(uint32_t width, uint32_t height, uint32_t index, uint32_t count);
 /* The local tiles (first, count — indices into the shard's tile list, which is also the order of its compact

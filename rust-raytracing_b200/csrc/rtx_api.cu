@@ -3,7 +3,13 @@
 // Host-side mirror of raytracing/scene.rs (Scene::new / add_object / render / render_to_image) and
 // raytracing/camera.rs (Camera::new / set_direction / to_*_space).  The hot path itself lives in
 // rtx_render.cu; nothing here computes a pixel on the CPU.
+#include <fcntl.h>
+#include <sys/mman.h>
+#include <sys/stat.h>
+#include <unistd.h>
+
 #include <algorithm>
+#include <cerrno>
 #include <chrono>
 #include <cmath>
 #include <cstdlib>
@@ -219,6 +225,25 @@ static void shard_band_tiles(uint32_t width, uint32_t height, uint32_t index, ui
   *first = (uint32_t)local_below(lo);
   *n = (uint32_t)(local_below(hi) - local_below(lo));
 }
+// RTX_FLAG_SHARD_ROWS: the ownership unit is a full-width strip of GRAN_H (4) pixel rows, strip s -> shard s mod count.
+static uint64_t strip_count(uint32_t height) { return ((uint64_t)height + GRAN_H - 1) / GRAN_H; }
+static uint64_t shard_strips(uint32_t height, uint32_t index, uint32_t count) {
+  if (count == 0 || index >= count) return 0;
+  const uint64_t strips = strip_count(height);
+  return index >= strips ? 0 : (strips - index + count - 1) / count;
+}
+// The same band of tile rows — pixel rows [16 row_first, 16 (row_first + row_count)) — as a range of LOCAL strips.
+static void shard_band_strips(uint32_t height, uint32_t index, uint32_t count, uint32_t row_first, uint32_t row_count,
+                              uint32_t* first, uint32_t* n) {
+  *first = 0, *n = 0;
+  if (count == 0 || index >= count) return;
+  const uint64_t strips = strip_count(height), per_row = TILE / GRAN_H;
+  const uint64_t lo = std::min<uint64_t>((uint64_t)row_first * per_row, strips);
+  const uint64_t hi = std::min<uint64_t>(((uint64_t)row_first + row_count) * per_row, strips);
+  auto local_below = [&](uint64_t g) { return g > index ? (g - index + count - 1) / count : 0ull; };
+  *first = (uint32_t)local_below(lo);
+  *n = (uint32_t)(local_below(hi) - local_below(lo));
+}
 
 // ---- small device kernels owned by the API layer ------------------------------------------------
 // ≙ the row-ordered join of scene.rs:167-169: scatter gathered per-rank tile buffers into the image.
@@ -333,8 +358,11 @@ static rtx_status render_common_on_stream(rtx_scene* s, uint32_t width, uint32_t
   fill_bvh_view(s, use_bvh, &p.bvh);
   p.shard_index = sh.index, p.shard_count = sh.count;
   p.tiles_x = (width + TILE - 1) / TILE, p.tiles_y = (height + TILE - 1) / TILE;
-  p.my_tiles = (uint32_t)shard_tiles(width, height, sh.index, sh.count);
-  p.compact = (sh.count > 1 && !(flags & RTX_FLAG_SHARD_IN_PLACE)) ? 1u : 0u;
+  const bool strips = (flags & RTX_FLAG_SHARD_ROWS) != 0;
+  p.strip_mode = strips ? 1u : 0u;
+  p.grans_per_unit = strips ? (width + GRAN_W - 1) / GRAN_W : GRANS_PER_TILE;
+  p.my_tiles = strips ? (uint32_t)shard_strips(height, sh.index, sh.count) : (uint32_t)shard_tiles(width, height, sh.index, sh.count);
+  p.compact = (sh.count > 1 && !(flags & (RTX_FLAG_SHARD_IN_PLACE | RTX_FLAG_SHARD_ROWS))) ? 1u : 0u;
   p.work_counter = d_work_counter;
   p.out_rgb = (flags & RTX_FLAG_NO_RADIANCE) ? nullptr : d_rgb;
   p.out_ids = d_ids;
@@ -343,10 +371,11 @@ static rtx_status render_common_on_stream(rtx_scene* s, uint32_t width, uint32_t
   if (tile_rows) {
     // tile t of the image belongs to shard t mod count as its local tile t div count: a band of tile rows is a
     // contiguous range of local tiles
-    shard_band_tiles(width, height, sh.index, sh.count, tile_rows[0], tile_rows[1], &p.tile_first, &p.my_tiles);
+    if (strips) shard_band_strips(height, sh.index, sh.count, tile_rows[0], tile_rows[1], &p.tile_first, &p.my_tiles);
+    else shard_band_tiles(width, height, sh.index, sh.count, tile_rows[0], tile_rows[1], &p.tile_first, &p.my_tiles);
   }
   if (p.my_tiles == 0) return RTX_OK;
-  p.tail_first = p.my_tiles * GRANS_PER_TILE, p.tail_granules = 0, p.tail_scratch = nullptr;
+  p.tail_first = p.my_tiles * p.grans_per_unit, p.tail_granules = 0, p.tail_scratch = nullptr;
   const bool pool = !p.lane_kernel && pool_kernel_eligible(p);
   // A large frame bound for pinned host memory: bands of tile rows, each rendered with the sample queue into the
   // scene's device frame and copied out by the copy engine while the next band renders (C2 e2e 12.2 -> 11.5 ms
@@ -366,8 +395,8 @@ static rtx_status render_common_on_stream(rtx_scene* s, uint32_t width, uint32_t
       const uint32_t r0 = (uint32_t)((uint64_t)p.tiles_y * (2ull * b) / den);
       const uint32_t r1 = b + 1 == bands ? p.tiles_y : (uint32_t)((uint64_t)p.tiles_y * (2ull * (b + 1)) / den);
       if (r1 == r0) continue;
-      p.tile_first = r0 * p.tiles_x;
-      p.my_tiles = (r1 - r0) * p.tiles_x;
+      if (strips) shard_band_strips(height, 0, 1, r0, r1 - r0, &p.tile_first, &p.my_tiles);
+      else p.tile_first = r0 * p.tiles_x, p.my_tiles = (r1 - r0) * p.tiles_x;
       const size_t need = pool_plan_tail(p, s->sm_count);
       if (need) {
         RTX_CUDA_TRY(s, grow(&s->d_tail, &s->d_tail_cap, need));
@@ -839,6 +868,119 @@ rtx_status rtx_scene_render_device_band(rtx_scene* s, uint32_t width, uint32_t h
                                       (unsigned long long*)d_out_counters, wc, (cudaStream_t)cuda_stream, &launches, nullptr, rows);
   s->last_launches = launches;
   return st;
+}
+
+// Every GPU delivers ITS OWN pixels to their final place in one host frame, over its own PCIe link: the shard is cut
+// by rows (RTX_FLAG_SHARD_ROWS), rendered band by band into the scene's device frame, and after each band the copy
+// engine moves the band's strips — whole rows of the frame — to host memory with one 2-D copy (row pitch = count
+// strips) while the next band renders.  No rank-0 funnel, no collective on the data path.
+rtx_status rtx_scene_render_rows_to_host(rtx_scene* s, uint32_t width, uint32_t height, uint64_t seed, uint32_t flags,
+                                         const rtx_shard* shard, double* host_rgb, uint32_t* host_ids, void* d_out_counters,
+                                         void* cuda_stream) {
+  if (!s) return fail(s, RTX_ERR_INVALID_ARGUMENT, "null scene");
+  if (!host_rgb || (flags & RTX_FLAG_NO_RADIANCE)) return fail(s, RTX_ERR_INVALID_ARGUMENT, "host_rgb is required");
+  if (width == 0 || height == 0 || (uint64_t)width * height > 0xFFFFFFFFull)
+    return fail(s, RTX_ERR_INVALID_ARGUMENT, "bad image size");
+  rtx_shard sh{0, 1};
+  if (shard) sh = *shard;
+  if (sh.count == 0 || sh.index >= sh.count) return fail(s, RTX_ERR_INVALID_ARGUMENT, "invalid shard");
+  std::lock_guard<std::mutex> lk(s->mu);
+  RTX_CUDA_TRY(s, cudaSetDevice(s->device));
+  cudaStream_t stream = (cudaStream_t)cuda_stream;
+  const size_t npix = (size_t)width * height;
+  RTX_CUDA_TRY(s, grow(&s->d_rgb, &s->d_rgb_cap, npix * 3 * sizeof(double)));
+  if (host_ids) RTX_CUDA_TRY(s, grow(&s->d_ids, &s->d_ids_cap, npix * sizeof(uint32_t)));
+  if (!s->copy_stream) RTX_CUDA_TRY(s, cudaStreamCreateWithFlags(&s->copy_stream, cudaStreamNonBlocking));
+  for (cudaEvent_t& ev : s->ev_band)
+    if (!ev) RTX_CUDA_TRY(s, cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
+  const uint32_t tiles_y = (height + TILE - 1) / TILE;
+  // bands of tile rows, the last one half as tall (its copy is the one nothing overlaps); small shards: fewer bands
+  const uint64_t my_pixels = shard_strips(height, sh.index, sh.count) * GRAN_H * (uint64_t)width;
+  uint32_t bands = my_pixels >= (1u << 18) ? 4u : (my_pixels >= (1u << 16) ? 2u : 1u);
+  bands = std::min(bands, tiles_y);
+  const uint64_t strips = strip_count(height);
+  const size_t strip_elems = (size_t)GRAN_H * width;  // pixels of a full strip
+  uint32_t launches = 0;
+  const uint32_t fl = (flags & ~(uint32_t)RTX_FLAG_SHARD_IN_PLACE) | RTX_FLAG_SHARD_ROWS;
+  for (uint32_t b = 0; b < bands; ++b) {
+    const uint64_t den = 2ull * bands - 1ull;
+    const uint32_t r0 = (uint32_t)((uint64_t)tiles_y * (2ull * b) / den);
+    const uint32_t r1 = b + 1 == bands ? tiles_y : (uint32_t)((uint64_t)tiles_y * (2ull * (b + 1)) / den);
+    uint32_t first = 0, n = 0;
+    shard_band_strips(height, sh.index, sh.count, r0, r1 - r0, &first, &n);
+    if (n == 0) continue;
+    const uint32_t rows[2] = {r0, r1 - r0};
+    const rtx_status st = render_common(s, width, height, seed, fl, &sh, s->d_rgb, host_ids ? s->d_ids : nullptr,
+                                        (unsigned long long*)d_out_counters, s->d_work_counter + 2u * (s->wc_slot++ & 63u), stream,
+                                        &launches, nullptr, rows);
+    if (st != RTX_OK) return st;
+    RTX_CUDA_TRY(s, cudaEventRecord(s->ev_band[b], stream));
+    RTX_CUDA_TRY(s, cudaStreamWaitEvent(s->copy_stream, s->ev_band[b], 0));
+    // local strips [first, first + n) are the image's strips (first + j) * count + index: a 2-D copy whose "rows" are
+    // strips and whose pitch is `count` strips; a ragged last strip of the image goes separately
+    const uint64_t g0 = (uint64_t)first * sh.count + sh.index, g_last = (uint64_t)(first + n - 1) * sh.count + sh.index;
+    const bool ragged = g_last == strips - 1 && (height % GRAN_H) != 0;
+    const uint32_t full = ragged ? n - 1 : n;
+    if (full) {
+      RTX_CUDA_TRY(s, cudaMemcpy2DAsync(host_rgb + g0 * strip_elems * 3, (size_t)sh.count * strip_elems * 24,
+                                        s->d_rgb + g0 * strip_elems * 3, (size_t)sh.count * strip_elems * 24, strip_elems * 24, full,
+                                        cudaMemcpyDeviceToHost, s->copy_stream));
+      if (host_ids)
+        RTX_CUDA_TRY(s, cudaMemcpy2DAsync(host_ids + g0 * strip_elems, (size_t)sh.count * strip_elems * 4, s->d_ids + g0 * strip_elems,
+                                          (size_t)sh.count * strip_elems * 4, strip_elems * 4, full, cudaMemcpyDeviceToHost,
+                                          s->copy_stream));
+    }
+    if (ragged) {
+      const size_t px0 = g_last * strip_elems, px = npix - px0;
+      RTX_CUDA_TRY(s, cudaMemcpyAsync(host_rgb + px0 * 3, s->d_rgb + px0 * 3, px * 24, cudaMemcpyDeviceToHost, s->copy_stream));
+      if (host_ids)
+        RTX_CUDA_TRY(s, cudaMemcpyAsync(host_ids + px0, s->d_ids + px0, px * 4, cudaMemcpyDeviceToHost, s->copy_stream));
+    }
+  }
+  // the caller's stream is done when the last copy is (and so is the scene's device frame, for the next render)
+  RTX_CUDA_TRY(s, cudaEventRecord(s->ev_band[rtx_scene::MAX_BANDS], s->copy_stream));
+  RTX_CUDA_TRY(s, cudaStreamWaitEvent(stream, s->ev_band[rtx_scene::MAX_BANDS], 0));
+  if (s->ev_last && cudaEventRecord(s->ev_last, stream) == cudaSuccess) s->last_stream = stream, s->last_valid = true;
+  s->last_launches = launches;
+  return RTX_OK;
+}
+
+// ---- one pinned host frame shared by the processes of a node (POSIX shared memory + cudaHostRegister) -------------
+static rtx_status host_frame_map(const char* name, uint64_t bytes, bool create, void** out) {
+  if (!name || !out || bytes == 0) return fail(nullptr, RTX_ERR_INVALID_ARGUMENT, "bad host frame arguments");
+  *out = nullptr;
+  const int fd = shm_open(name, create ? (O_CREAT | O_EXCL | O_RDWR) : O_RDWR, 0600);
+  if (fd < 0) return fail(nullptr, RTX_ERR_INVALID_ARGUMENT, std::string("shm_open(") + name + ") failed: " + std::strerror(errno));
+  if (create && ftruncate(fd, (off_t)bytes) != 0) {
+    const std::string why = std::strerror(errno);
+    close(fd);
+    shm_unlink(name);
+    return fail(nullptr, RTX_ERR_OUT_OF_MEMORY, "ftruncate of the host frame failed: " + why);
+  }
+  void* p = mmap(nullptr, bytes, PROT_READ | PROT_WRITE, MAP_SHARED | MAP_POPULATE, fd, 0);
+  close(fd);
+  if (p == MAP_FAILED) {
+    if (create) shm_unlink(name);
+    return fail(nullptr, RTX_ERR_OUT_OF_MEMORY, std::string("mmap of the host frame failed: ") + std::strerror(errno));
+  }
+  const cudaError_t e = cudaHostRegister(p, bytes, cudaHostRegisterPortable);
+  if (e != cudaSuccess) {
+    munmap(p, bytes);
+    if (create) shm_unlink(name);
+    return cuda_fail(nullptr, e, "cudaHostRegister of the host frame");
+  }
+  *out = p;
+  return RTX_OK;
+}
+rtx_status rtx_host_frame_create(const char* name, uint64_t bytes, void** out) { return host_frame_map(name, bytes, true, out); }
+rtx_status rtx_host_frame_open(const char* name, uint64_t bytes, void** out) { return host_frame_map(name, bytes, false, out); }
+rtx_status rtx_host_frame_close(void* ptr, uint64_t bytes, const char* unlink_name) {
+  if (ptr) {
+    if (cudaHostUnregister(ptr) != cudaSuccess) cudaGetLastError();
+    munmap(ptr, bytes);
+  }
+  if (unlink_name) shm_unlink(unlink_name);
+  return RTX_OK;
 }
 
 rtx_status rtx_scene_render(rtx_scene* s, uint32_t width, uint32_t height, uint64_t seed, uint32_t flags,

@@ -100,6 +100,7 @@ extern "C" rtx_status rtx_scene_render_device_noalloc(rtx_scene* s, uint32_t wid
   p.shard_index = 0, p.shard_count = 1;
   p.tiles_x = (width + TILE - 1) / TILE, p.tiles_y = (height + TILE - 1) / TILE;
   p.my_tiles = p.tiles_x * p.tiles_y;
+  p.grans_per_unit = GRANS_PER_TILE;
   p.work_counter = reinterpret_cast<uint32_t*>(scratch);
   p.out_rgb = static_cast<double*>(d_out_rgb);
   p.out_ids = static_cast<uint32_t*>(d_out_primary_hit_id);

@@ -56,7 +56,7 @@ __global__ void __launch_bounds__(RENDER_BLOCK, USE_BVH ? BVH_BLOCKS_PER_SM : 2)
   to_world.z = mk3(p.to_world[6], p.to_world[7], p.to_world[8]);
   const uint64_t rpp = p.rays_per_pixel;
   const uint64_t max_segments = p.max_bounces + 1ull;  // scene.rs:227
-  const uint32_t total_work = p.my_tiles * GRANS_PER_TILE;
+  const uint32_t total_work = p.my_tiles * p.grans_per_unit;
 
   // warp-uniform queue state
   uint32_t g_x0 = 0, g_y0 = 0, g_w = 0, g_npix = 0, g_next = 0, g_base_out = 0, g_tx0 = 0, g_ty0 = 0;
@@ -90,19 +90,9 @@ __global__ void __launch_bounds__(RENDER_BLOCK, USE_BVH ? BVH_BLOCKS_PER_SM : 2)
           exhausted = true;
           break;
         }
-        const uint32_t ltile = p.tile_first + w / GRANS_PER_TILE, sub = w % GRANS_PER_TILE;
-        const uint32_t gtile = ltile * p.shard_count + p.shard_index;
-        const uint32_t ty = gtile / p.tiles_x, tx = gtile % p.tiles_x;
-        g_tx0 = tx * TILE;
-        g_ty0 = ty * TILE;
-        g_x0 = g_tx0 + (sub % (TILE / GRAN_W)) * GRAN_W;
-        g_y0 = g_ty0 + (sub / (TILE / GRAN_W)) * GRAN_H;
-        const uint32_t gw = g_x0 < p.width ? min(GRAN_W, p.width - g_x0) : 0u;
-        const uint32_t gh = g_y0 < p.height ? min(GRAN_H, p.height - g_y0) : 0u;
-        g_w = gw;
-        g_npix = gw * gh;
+        const Granule g = decode_granule(p, w);
+        g_tx0 = g.tx0, g_ty0 = g.ty0, g_x0 = g.x0, g_y0 = g.y0, g_w = g.w, g_npix = g.npix, g_base_out = g.base_out;
         g_next = 0;
-        g_base_out = ltile * (TILE * TILE);
         continue;  // re-check (granule may be empty at the image border)
       }
       const uint32_t slot = g_next + __popc(need & lt_mask);
@@ -231,7 +221,7 @@ cudaError_t launch_render(const RenderParams& p, int sm_count, cudaStream_t stre
   const size_t smem = use_smem ? (size_t)p.layout.bytes + 128 : 0;
   cudaError_t e = cudaSuccess;
   const int blocks_per_sm = p.use_bvh ? BVH_BLOCKS_PER_SM : 2;
-  const uint64_t total_work = (uint64_t)p.my_tiles * GRANS_PER_TILE;
+  const uint64_t total_work = (uint64_t)p.my_tiles * p.grans_per_unit;
   // persistent grid: a multiple of the SM count, never more warps than granules
   uint64_t want_blocks = (total_work + (RENDER_BLOCK / 32) - 1) / (RENDER_BLOCK / 32);
   uint64_t grid = (uint64_t)sm_count * blocks_per_sm;

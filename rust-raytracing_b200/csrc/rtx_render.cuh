@@ -37,9 +37,14 @@ struct RenderParams {
   // image shard
   uint32_t shard_index, shard_count;
   uint32_t tiles_x, tiles_y;
-  uint32_t my_tiles;    // tiles of this shard this launch renders ...
-  uint32_t tile_first;  // ... starting at this one (a band of the shard's tile list; 0 = from the start)
+  uint32_t my_tiles;    // ownership units (tiles, or strips) of this shard this launch renders ...
+  uint32_t tile_first;  // ... starting at this one (a band of the shard's unit list; 0 = from the start)
   uint32_t compact;     // 1: outputs use the compact per-shard tile layout
+  // Ownership unit.  0: RTX_TILE x RTX_TILE tiles, row-major, 8 granules each (the default: the best load balance).
+  // 1 (RTX_FLAG_SHARD_ROWS): full-width STRIPS of GRAN_H = 4 pixel rows, strip s -> shard s mod count — a shard's
+  // pixels are whole contiguous rows of the frame, which a copy engine moves to host memory with one 2-D copy per band.
+  uint32_t strip_mode;
+  uint32_t grans_per_unit;  // GRANS_PER_TILE, or ceil(width / GRAN_W) in strip mode
   // The atomic work queue: [0] next entry, [1] CTAs that have left the queue.  Both are zero when a launch starts and
   // the launch leaves them zero (queue_release: the last CTA out resets them) — no memset between frames, which in
   // the launch-bound regime (C5 at 256x256) was one of the three stream operations of a frame.
@@ -62,9 +67,20 @@ struct RenderParams {
 struct Granule {
   uint32_t x0, y0, w, npix, base_out, tx0, ty0;
 };
-// gidx = index of the granule within this shard's tile list (local tile = gidx / GRANS_PER_TILE).
+// gidx = index of the granule within this shard's unit list (local unit = gidx / grans_per_unit).
 __device__ __forceinline__ Granule decode_granule(const RenderParams& p, uint32_t gidx) {
   Granule g;
+  if (p.strip_mode) {  // (warp-uniform)
+    const uint32_t lstrip = p.tile_first + gidx / p.grans_per_unit, col = gidx % p.grans_per_unit;
+    g.tx0 = g.ty0 = g.base_out = 0;
+    g.x0 = col * GRAN_W;
+    g.y0 = (lstrip * p.shard_count + p.shard_index) * GRAN_H;
+    const uint32_t gw = g.x0 < p.width ? min(GRAN_W, p.width - g.x0) : 0u;
+    const uint32_t gh = g.y0 < p.height ? min(GRAN_H, p.height - g.y0) : 0u;
+    g.w = gw;
+    g.npix = gw * gh;
+    return g;
+  }
   const uint32_t ltile = p.tile_first + gidx / GRANS_PER_TILE, sub = gidx % GRANS_PER_TILE;
   const uint32_t gtile = ltile * p.shard_count + p.shard_index;
   const uint32_t ty = gtile / p.tiles_x, tx = gtile % p.tiles_x;

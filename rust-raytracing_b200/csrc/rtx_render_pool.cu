@@ -417,7 +417,7 @@ bool pool_kernel_eligible(const RenderParams& p) {
 // RTX_FLAG_PIXEL_QUEUE / RTX_FLAG_SAMPLE_QUEUE force one.  The image is the same either way.
 // Returns the scratch bytes needed (0 = pixel queue): [granules * rpp * 32 * 3] f64 + [granules * rpp * 32] flag bytes.
 size_t pool_plan_tail(RenderParams& p, int sm_count) {
-  const uint64_t granules = (uint64_t)p.my_tiles * GRANS_PER_TILE;
+  const uint64_t granules = (uint64_t)p.my_tiles * p.grans_per_unit;
   p.tail_first = (uint32_t)granules;
   p.tail_granules = 0;
   p.tail_scratch = nullptr;

@@ -19,12 +19,13 @@ import numpy as np
 
 from . import _abi
 from ._abi import (MISS_ID, RTX_ACCEL_AUTO, RTX_ACCEL_BRUTE, RTX_ACCEL_LBVH, RTX_FLAG_LANE_KERNEL, RTX_FLAG_NO_RADIANCE,
-                   RTX_FLAG_PIXEL_QUEUE, RTX_FLAG_SAMPLE_QUEUE, RTX_FLAG_SHARD_IN_PLACE, RTX_TILE, RtxError,
+                   RTX_FLAG_PIXEL_QUEUE, RTX_FLAG_SAMPLE_QUEUE, RTX_FLAG_SHARD_IN_PLACE, RTX_FLAG_SHARD_ROWS, RTX_TILE, RtxError,
                    Shard, Stats)
 
 __all__ = ["Vector3", "Camera", "Config", "Material", "Sphere", "Plane", "Triangle", "Object", "Scene", "RtxError",
+           "HostFrame", "MultiScene",
            "MISS_ID", "RTX_ACCEL_AUTO", "RTX_ACCEL_BRUTE", "RTX_ACCEL_LBVH", "RTX_FLAG_LANE_KERNEL", "RTX_FLAG_NO_RADIANCE",
-           "RTX_FLAG_PIXEL_QUEUE", "RTX_FLAG_SAMPLE_QUEUE", "RTX_FLAG_SHARD_IN_PLACE", "RTX_TILE",
+           "RTX_FLAG_PIXEL_QUEUE", "RTX_FLAG_SAMPLE_QUEUE", "RTX_FLAG_SHARD_IN_PLACE", "RTX_FLAG_SHARD_ROWS", "RTX_TILE",
            "device_count", "probe_fp64_peak", "shard_tile_count"]
 
 SHAPE_SPHERE, SHAPE_PLANE, SHAPE_TRIANGLE = 0, 1, 2
@@ -476,6 +477,15 @@ class Scene:
         h = self._sync()
         _abi.check(_abi.load().rtx_scene_render_device_noalloc(h, width, height, seed, flags, d_rgb, d_ids, stream), h)
 
+    def render_rows_to_host(self, width, height, seed, flags, shard, host_rgb_ptr, host_ids_ptr, d_counters, stream):
+        """rtx_scene_render_rows_to_host: this shard's rows (strips of 4, RTX_FLAG_SHARD_ROWS) rendered in bands and
+        delivered by this GPU's copy engine to their place in the whole-frame host buffer.  Asynchronous on `stream`."""
+        h = self._sync()
+        sh = Shard(*shard) if shard is not None else None
+        _abi.check(_abi.load().rtx_scene_render_rows_to_host(h, width, height, seed, flags,
+                                                             C.byref(sh) if sh is not None else None, host_rgb_ptr,
+                                                             host_ids_ptr, d_counters, stream), h)
+
     def render_device_band(self, width, height, seed, flags, shard, tile_row_first, tile_row_count, d_rgb, d_ids,
                            d_counters, stream):
         """render_device for the band of 16-pixel tile rows [tile_row_first, tile_row_first + tile_row_count) only."""
@@ -560,3 +570,62 @@ def debug_contraction_probe(a, b, c, device=0):
 
 def stream_state(seed, key):
     return _abi.load().rtx_stream_state(seed, key)
+
+
+class HostFrame:
+    """One pinned host frame [height][width][3] f64 shared by the processes of a node (rtx_host_frame_*: POSIX shared
+    memory registered with CUDA in every process).  create=True on one rank, False on the others (after the creator)."""
+
+    def __init__(self, name, width, height, create):
+        self.name, self.width, self.height, self.creator = name.encode(), width, height, bool(create)
+        self.bytes = width * height * 24
+        p = C.c_void_p()
+        fn = _abi.load().rtx_host_frame_create if create else _abi.load().rtx_host_frame_open
+        _abi.check(fn(self.name, self.bytes, C.byref(p)))
+        self.ptr = int(p.value)
+        self.array = np.ctypeslib.as_array((C.c_double * (width * height * 3)).from_address(self.ptr)).reshape(height, width, 3)
+
+    def close(self):
+        if self.ptr:
+            self.array = None
+            _abi.check(_abi.load().rtx_host_frame_close(C.c_void_p(self.ptr), self.bytes, self.name if self.creator else None))
+            self.ptr = 0
+
+
+class MultiScene:
+    """rtx_multi_*: N GPUs of this process behind one handle; render() blocks and returns the whole image on the host
+    (≙ Scene::render, scene.rs:144-170).  Objects are taken from a Scene built the usual way."""
+
+    def __init__(self, scene, devices):
+        lib = _abi.load()
+        self.devices = list(devices)
+        dev = (C.c_int32 * len(self.devices))(*self.devices)
+        cfg = scene.config._c()
+        h = C.c_void_p()
+        _abi.check(lib.rtx_multi_create(C.byref(scene.camera._c), C.byref(cfg), dev, len(self.devices), C.byref(h)))
+        self._handle = h
+        add = {SHAPE_SPHERE: lib.rtx_multi_add_spheres, SHAPE_PLANE: lib.rtx_multi_add_planes,
+               SHAPE_TRIANGLE: lib.rtx_multi_add_triangles}
+        for kind, s, m in scene._batches:
+            _abi.check(add[kind](h, s.ctypes.data, m.ctypes.data, s.shape[0]))
+        self.last_stats = None
+
+    def render(self, width, height, seed=0, flags=RTX_ACCEL_AUTO, out=None, want_ids=False):
+        rgb = out if out is not None else np.empty((height, width, 3), dtype=np.float64)
+        ids = np.empty((height, width), dtype=np.uint32) if want_ids else None
+        st = Stats()
+        _abi.check(_abi.load().rtx_multi_render(self._handle, width, height, seed, flags, rgb.ctypes.data,
+                                                ids.ctypes.data if ids is not None else None, C.byref(st)))
+        self.last_stats = st
+        return (rgb, ids) if want_ids else rgb
+
+    def close(self):
+        if self._handle is not None:
+            _abi.check(_abi.load().rtx_multi_destroy(self._handle))
+            self._handle = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass

@@ -77,6 +77,7 @@ RTX_FLAG_LANE_KERNEL = 8
 RTX_FLAG_SHARD_IN_PLACE = 16
 RTX_FLAG_PIXEL_QUEUE = 32
 RTX_FLAG_SAMPLE_QUEUE = 64
+RTX_FLAG_SHARD_ROWS = 128
 RTX_PEER_HANDLE_BYTES = 64
 RTX_TILE = 16
 RTX_NOALLOC_SCRATCH_BYTES = 32 << 20
@@ -117,6 +118,22 @@ SIGNATURES = {
     "rtx_scene_render_device_band": (C.c_int32, [_vp, C.c_uint32, C.c_uint32, C.c_uint64, C.c_uint32, _P(Shard),
                                                  C.c_uint32, C.c_uint32, _vp, _vp, _vp, _vp]),
     "rtx_scene_render_device_noalloc": (C.c_int32, [_vp, C.c_uint32, C.c_uint32, C.c_uint64, C.c_uint32, _vp, _vp, _vp]),
+    "rtx_scene_render_rows_to_host": (C.c_int32, [_vp, C.c_uint32, C.c_uint32, C.c_uint64, C.c_uint32, _P(Shard), _vp, _vp,
+                                                  _vp, _vp]),
+    "rtx_host_frame_create": (C.c_int32, [C.c_char_p, C.c_uint64, _P(_vp)]),
+    "rtx_host_frame_open": (C.c_int32, [C.c_char_p, C.c_uint64, _P(_vp)]),
+    "rtx_host_frame_close": (C.c_int32, [_vp, C.c_uint64, C.c_char_p]),
+    "rtx_multi_create": (C.c_int32, [_P(CameraC), _P(ConfigC), _P(C.c_int32), C.c_uint32, _P(_vp)]),
+    "rtx_multi_destroy": (C.c_int32, [_vp]),
+    "rtx_multi_device_count": (C.c_uint32, [_vp]),
+    "rtx_multi_scene": (_vp, [_vp, C.c_uint32]),
+    "rtx_multi_set_camera": (C.c_int32, [_vp, _P(CameraC)]),
+    "rtx_multi_set_config": (C.c_int32, [_vp, _P(ConfigC)]),
+    "rtx_multi_add_spheres": (C.c_int32, [_vp, _vp, _vp, C.c_uint64]),
+    "rtx_multi_add_planes": (C.c_int32, [_vp, _vp, _vp, C.c_uint64]),
+    "rtx_multi_add_triangles": (C.c_int32, [_vp, _vp, _vp, C.c_uint64]),
+    "rtx_multi_clear_objects": (C.c_int32, [_vp]),
+    "rtx_multi_render": (C.c_int32, [_vp, C.c_uint32, C.c_uint32, C.c_uint64, C.c_uint32, _vp, _vp, _P(Stats)]),
     "rtx_shard_band_tiles": (None, [C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32,
                                     _P(C.c_uint32), _P(C.c_uint32)]),
     "rtx_shard_tile_count": (C.c_uint64, [C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32]),
