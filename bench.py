@@ -29,12 +29,15 @@ sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.join(ROOT, "rust-raytracing_b200"))
 
 WIDTH, HEIGHT, SPP, MAX_BOUNCES, SEED = 1920, 1080, 64, 8, 1
-# one `ncu --set full` capture of render_pool_kernel<64,1,true,24> on this workload (profiles/r01_render_pool_kernel_v6_raw.csv)
-NCU_TRAFFIC = 457520000 + 674960000
-NCU_TRAFFIC_SOURCE = ("bytes per launch, dram__bytes_read.sum 457.5 MB + dram__bytes_write.sum 675.0 MB of one ncu capture of "
-                      "render_pool_kernel<64,1,true,24> on this workload (profiles/r01_SUMMARY.md): the sample queue's scratch is a "
-                      "flag byte per camera path (132.7 MB) + 24 B of radiance for the 21 % of paths whose radiance is not zero; "
-                      "tail_sum_kernel then reads 1.27 GB in 0.235 ms (5.4 TB/s) and writes the 49.8 MB frame")
+# one `ncu --set full` capture of render_pool_kernel<64,1,true,24,false> on this workload in round 2
+# (profiles/r02_render_pool_kernel_raw.csv: dram__bytes_read.sum 458.63 MB, dram__bytes_write.sum 675.98 MB)
+NCU_TRAFFIC = 458631936 + 675983616
+NCU_TRAFFIC_SOURCE = ("bytes per launch, dram__bytes_read.sum 458.6 MB + dram__bytes_write.sum 676.0 MB of one ncu capture of "
+                      "render_pool_kernel<64,1,true,24,false> on this workload (profiles/r02_render_pool_kernel_raw.csv): the sample "
+                      "queue's scratch is a flag byte per camera path (132.7 MB) + 24 B of radiance for the 21 % of paths whose "
+                      "radiance is not zero; the reads are sector fills of those partial writes; tail_sum_kernel then reads 1.27 GB "
+                      "in 0.235 ms (5.4 TB/s) and writes the 49.8 MB frame.  Over the 10 ms launch that is 0.11 TB/s: DRAM is not "
+                      "what bounds this kernel (DESIGN.md 4.2)")
 METRIC = "Mrays/s at 1080p 64spp, 1/2/4/8 B200, vs ref CPU path on host cores"
 WORKLOAD = "S1 sphere demo scene (1 plane + 6 spheres), 1920x1080, 64 spp, max depth 8 (BASELINE.json configs[1])"
 
@@ -429,7 +432,20 @@ def run_b200(args):
     # ---- e2e: the public host-buffer API, pinned host memory, copies inside the timed region ----
     e2e = None
     npix = W * H
-    pin = torch.empty((H, W, 3), dtype=torch.float64).pin_memory() if rank == 0 else None
+    host_frame = None
+    if world > 1 and args.gather == "p2p":
+        # ONE pinned host frame in shared memory, mapped by every rank: each rank's copy engine delivers its own rows
+        # over its own PCIe link (rtx_scene_render_rows_to_host) — no rank-0 funnel
+        names = [f"/rtx-bench-{os.getpid()}"]
+        dist.broadcast_object_list(names, src=0)
+        if rank == 0:
+            host_frame = rtx_b200.HostFrame(names[0], W, H, create=True)
+        dist.barrier()
+        if rank != 0:
+            host_frame = rtx_b200.HostFrame(names[0], W, H, create=False)
+        pin = torch.from_numpy(host_frame.array) if rank == 0 else None
+    else:
+        pin = torch.empty((H, W, 3), dtype=torch.float64).pin_memory() if rank == 0 else None
     types, shapes, mats = scene.objects_flat()
     e2e_rays = [0]
 
@@ -445,8 +461,12 @@ def run_b200(args):
             e2e_rays[0] += scene.last_stats.rays
             return
         if args.gather == "p2p":
-            # the frame goes to rank 0's pinned host memory band by band while the next band renders on every rank
-            frame.render_to_host(scene, seed, pin, counters)
+            # every rank renders its rows (strips of 4, interleaved over the ranks) band by band and its copy engine puts
+            # each band's rows at their place in the shared host frame while the next band renders; the 4-byte all-reduce
+            # is the stream-ordered completion barrier: behind it on rank 0's stream the frame is whole
+            scene.render_rows_to_host(W, H, seed, rtx_b200.RTX_ACCEL_AUTO, (rank, world), host_frame.ptr, None,
+                                      counters.data_ptr(), stream.cuda_stream)
+            dist.all_reduce(align)
             return
         out = step(seed)
         if rank == 0:
@@ -501,24 +521,39 @@ def run_b200(args):
     else:
         e2e_checked = None
 
+    e2e_rgb8 = None
+    if world == 1:
+        # the same step through rtx_scene_render_to_rgb8 (scene.rs:173-178 on the device): 3 bytes per pixel come back
+        img8 = None
+        for i in range(-1, K):
+            if i == 0:
+                torch.cuda.synchronize(dev)
+                t0 = time.perf_counter()
+            img8 = scene.render_to_image(W, H, seed=SEED + max(i, 0))
+        dt8 = time.perf_counter() - t0
+        e2e_rgb8 = {"value": rays / dt8 / 1e6, "unit": "Mrays/s", "ms_per_step": dt8 / K * 1e3, "d2h_bytes_per_step": int(npix * 3),
+                    "api": "rtx_scene_render_to_rgb8 (render + flip/x256/saturate on the device, uint8 image to host)"}
     blob_bytes = (len(types) * (8 * 8) + int((types == 0).sum()) * 36 +
                                              int((types == 1).sum()) * 84 + int((types == 2).sum()) * 116)
     e2e = {"value": e2e_total_rays / float(te.item()) / 1e6, "unit": "Mrays/s",
            "h2d_bytes_per_step": int(blob_bytes), "d2h_bytes_per_step": int(npix * 24 + 32),
            "api": "rtx_scene_render (host buffers, pinned)" if world == 1 else
-                  ("rtx_scene_render_device_band per rank (RTX_FLAG_SHARD_IN_PLACE into rank 0's peer frame) + banded D2H on rank 0"
-                   if args.gather == "p2p" else
+                  ("rtx_scene_render_rows_to_host per rank into one shared pinned host frame (rtx_host_frame_*): every GPU "
+                   "delivers its own rows over its own PCIe link" if args.gather == "p2p" else
                    "rtx_scene_render_device per rank + NCCL gather + rtx_deinterleave_tiles + D2H on rank 0"),
            "ms_per_step": float(te.item()) / K * 1e3, "frame_equals_device_frame": e2e_checked,
            "d2h": ("inside rtx_scene_render: the frame is rendered in 4 bands of tile rows into a device frame; each band's "
                    "cudaMemcpyAsync to the pinned caller buffer runs on a copy stream while the next band renders"
                    if world == 1 else
-                   ("PeerFrame.render_to_host: 4 bands; after a band's completion barrier rank 0's copy engine moves its rows to "
-                    "pinned host memory while every rank renders the next band" if args.gather == "p2p" else
+                   ("inside rtx_scene_render_rows_to_host on every rank: the rank's rows are rendered in bands into its own device "
+                    "frame; after each band one cudaMemcpy2DAsync moves the band's strips to the host frame on a copy stream "
+                    "while the next band renders; a 4-byte all-reduce per step is the completion barrier" if args.gather == "p2p" else
                     "cudaMemcpyAsync of rank 0's frame to pinned host memory after the step"))}
 
     if world > 1 and args.gather == "p2p":
         frame.close()
+        pin = None
+        host_frame.close()
 
     # ---- the other BASELINE.json configs (outside every timed region of the headline) ----
     peaks = {}
@@ -582,7 +617,7 @@ def run_b200(args):
                      "completion barrier, inside the step" if args.gather == "p2p" else "NCCL gather to rank 0 + de-interleave "
                      "kernel, inside the step"),
         "counts": {"rays_per_step": rays / K, "hits_per_step": hits / K, "paths_per_step": paths / K},
-        "e2e": e2e, "gpu_launches": launches_per_step * K, "roofline": roofline, "cpu_baseline": cpu_baseline,
+        "e2e": e2e, "e2e_rgb8": e2e_rgb8, "gpu_launches": launches_per_step * K, "roofline": roofline, "cpu_baseline": cpu_baseline,
         "nrank_equals_1rank": nrank_equals_1rank, "check_seed": check_seed,
         "other_configs": others,
         "clocks": clocks, "wall_s_timed_region": t_wall, "triangle_panics": panics,

@@ -896,7 +896,7 @@ rtx_status rtx_scene_render_rows_to_host(rtx_scene* s, uint32_t width, uint32_t 
   const uint32_t tiles_y = (height + TILE - 1) / TILE;
   // bands of tile rows, the last one half as tall (its copy is the one nothing overlaps); small shards: fewer bands
   const uint64_t my_pixels = shard_strips(height, sh.index, sh.count) * GRAN_H * (uint64_t)width;
-  uint32_t bands = my_pixels >= (1u << 18) ? 4u : (my_pixels >= (1u << 16) ? 2u : 1u);
+  uint32_t bands = my_pixels >= (1u << 19) ? 4u : (my_pixels >= (1u << 17) ? 3u : (my_pixels >= (1u << 15) ? 2u : 1u));
   bands = std::min(bands, tiles_y);
   const uint64_t strips = strip_count(height);
   const size_t strip_elems = (size_t)GRAN_H * width;  // pixels of a full strip

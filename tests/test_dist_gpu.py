@@ -60,6 +60,29 @@ def _worker(rank, world, port, w, h, q):
             q.put((bool(ok), bool(ok2), bool(ok3)))
         dist.barrier()
         frame.close()
+        # no rank-0 funnel: one pinned host frame in shared memory, every rank delivers its own rows over its own PCIe
+        # link (rtx_scene_render_rows_to_host); two frames back to back, then the completion barrier
+        from rtx_b200 import HostFrame
+        name = f"/rtx-test-dist-{port}"
+        hf = HostFrame(name, w, h, create=True) if rank == 0 else None
+        dist.barrier()
+        if rank != 0:
+            hf = HostFrame(name, w, h, create=False)
+        if rank == 0:
+            hf.array[:] = -1.0
+        dist.barrier()
+        st = torch.cuda.current_stream().cuda_stream
+        ok4 = True
+        for seed in (21, 22):
+            sc.render_rows_to_host(w, h, seed, 0, (rank, world), hf.ptr, None, None, st)
+            torch.cuda.synchronize()
+            dist.barrier()
+            if rank == 0:
+                ok4 = ok4 and hf.array.tobytes() == sc.render(w, h, seed=seed).tobytes()
+            dist.barrier()
+        hf.close()
+        if rank == 0:
+            q.put(bool(ok4))
     finally:
         dist.destroy_process_group()
 
@@ -81,3 +104,26 @@ def test_two_gpu_render_equals_one_gpu(rtx, gpu):
         p.join(300)
         assert p.exitcode == 0
     assert q.get(timeout=5) == (True, True, True)  # (NCCL gather path, fused peer-store path, banded hand-over to the host)
+    assert q.get(timeout=5) is True  # shared host frame, every rank delivering its own rows
+
+
+def test_multi_handle_two_gpus_equals_one_gpu(rtx, oracle, gpu):
+    """rtx_multi_*: both GPUs of this process behind one handle, no process group; the image is the one-GPU image and
+    the oracle's."""
+    if rtx.device_count() < 2:
+        pytest.skip("needs 2 GPUs (run with gpurun --gpus 2)")
+    import torch
+    from rtx_b200 import MultiScene, scenes
+    w, h = 1000, 562
+    sc = scenes.sphere_demo(rays_per_pixel=4, max_bounces=8)
+    m = MultiScene(sc, [0, 1])
+    pin = torch.full((h, w, 3), -1.0, dtype=torch.float64).pin_memory()
+    for seed in (5, 6, 7):
+        got, ids = m.render(w, h, seed=seed, out=pin.numpy(), want_ids=True)
+        ref, ref_ids = sc.render(w, h, seed=seed, want_ids=True)
+        assert got.tobytes() == ref.tobytes() and np.array_equal(ids, ref_ids), seed
+        assert m.last_stats.rays == sc.last_stats.rays
+    assert float(np.abs(got - oracle.render_scene(sc, w, h, seed=7)["rgb"]).max()) <= 1e-4
+    pageable = m.render(w, h, seed=7)  # a pageable caller buffer works too (slower copies)
+    assert pageable.tobytes() == ref.tobytes()
+    m.close()
