@@ -83,6 +83,11 @@ enum {
   RTX_FLAG_SAMPLE_QUEUE = 64u,    /* context-pool kernel: force (pixel, sample) queue entries + ordered sum
                                      pass (short tail: small images, multi-GPU shards).  Default: chosen
                                      from pixels per resident context.  Same image either way.         */
+  RTX_FLAG_RNG_ROW    = 256u,     /* the reference's literal RNG consumption: one stream per image ROW (≙ the row thread's
+                                     thread-local fastrand, scene.rs:149-161, math/vector.rs:29-45), every draw in the
+                                     reference's order, one CUDA thread per row.  A different image from the default
+                                     per-(pixel, sample) streams (only the seeding differs); slow by construction; whole
+                                     image only.  Bit-exact against the oracle's RNG_ROW mode.                        */
   RTX_FLAG_SHARD_ROWS = 128u,     /* shard by full-width STRIPS of 4 pixel rows (strip s belongs to shard s % count)
                                      instead of 16x16 tiles, written in place like RTX_FLAG_SHARD_IN_PLACE: a
                                      shard's pixels are whole contiguous rows of the frame, which each GPU's copy

@@ -374,6 +374,12 @@ static rtx_status render_common_on_stream(rtx_scene* s, uint32_t width, uint32_t
     if (strips) shard_band_strips(height, sh.index, sh.count, tile_rows[0], tile_rows[1], &p.tile_first, &p.my_tiles);
     else shard_band_tiles(width, height, sh.index, sh.count, tile_rows[0], tile_rows[1], &p.tile_first, &p.my_tiles);
   }
+  if (flags & RTX_FLAG_RNG_ROW) {
+    if (sh.count != 1 || tile_rows) return fail(s, RTX_ERR_INVALID_ARGUMENT, "RTX_FLAG_RNG_ROW renders the whole image: no shard, no band");
+    cudaError_t e = launch_render_rows(p, stream, launches);
+    if (e != cudaSuccess) return cuda_fail(s, e, "render_rows_kernel launch");
+    return RTX_OK;
+  }
   if (p.my_tiles == 0) return RTX_OK;
   p.tail_first = p.my_tiles * p.grans_per_unit, p.tail_granules = 0, p.tail_scratch = nullptr;
   const bool pool = !p.lane_kernel && pool_kernel_eligible(p);

@@ -103,6 +103,8 @@ rtx_status ensure_uploaded(rtx_scene* s, cudaStream_t stream);
 // Builds (or reuses) the sin/cos tables for this image size.  Asynchronous on `stream`.
 rtx_status ensure_tables(rtx_scene* s, uint32_t width, uint32_t height, cudaStream_t stream);
 cudaError_t launch_render(const RenderParams& p, int sm_count, cudaStream_t stream, uint32_t* out_launches);
+// RTX_FLAG_RNG_ROW: one thread per image row, one RNG stream per row (rtx_render.cu)
+cudaError_t launch_render_rows(const RenderParams& p, cudaStream_t stream, uint32_t* out_launches);
 // rtx_render_pool.cu: the context-pool kernel for scanned, shared-memory-resident scenes
 bool pool_kernel_eligible(const RenderParams& p);
 // Fills p.tail_first / p.tail_granules; returns the bytes p.tail_scratch must hold (0 = no tail region).

@@ -213,6 +213,91 @@ __global__ void __launch_bounds__(RENDER_BLOCK, USE_BVH ? BVH_BLOCKS_PER_SM : 2)
   queue_release(p);
 }
 
+// RTX_FLAG_RNG_ROW: the reference's own consumption of its random source, literally.  In Scene::render every row is
+// one thread (scene.rs:149-151) and every draw of that thread comes from its one thread-local generator, pixel after
+// pixel, sample after sample, bounce after bounce (math/vector.rs:29-45) — including the bounce directions whose ray is
+// never traced (ray_hit always draws, scene.rs:275; the other kernels skip those because their streams are private to
+// a camera path).  Here one CUDA thread is one row thread with one WyRand stream, state0 = stream_state(seed ^
+// "ROW_STRE", y) (the reference's seed is the clock).  It exists to show that the per-(pixel, sample) streams of the
+// production kernels differ from the literal reference in the SEEDING only: the oracle has the same mode
+// (oracle_render, RNG_ROW) and the two agree bit for bit.  A frame is `height` threads: a demonstration, not a fast path.
+constexpr uint64_t ROW_STREAM_TAG = 0x524F575F53545245ULL;
+template <bool USE_BVH>
+__global__ void __launch_bounds__(32) render_rows_kernel(const __grid_constant__ RenderParams p) {
+  const uint32_t y = blockIdx.x * blockDim.x + threadIdx.x;
+  uint32_t n_rays = 0, n_paths = 0, n_panics = 0, n_hits = 0;
+  TraversalCounters tc;
+  tc.nodes = 0, tc.prims = 0;
+  const SceneView sc = make_view(p.scene_blob, p.layout);
+  if (y < p.height) {
+    const V3 cam_pos = mk3(p.cam_pos[0], p.cam_pos[1], p.cam_pos[2]);
+    M3 to_world;
+    to_world.x = mk3(p.to_world[0], p.to_world[1], p.to_world[2]);
+    to_world.y = mk3(p.to_world[3], p.to_world[4], p.to_world[5]);
+    to_world.z = mk3(p.to_world[6], p.to_world[7], p.to_world[8]);
+    WyRand rng;
+    rng.s = stream_state(p.seed ^ ROW_STREAM_TAG, y);
+    for (uint32_t x = 0; x < p.width; ++x) {
+      const V3 cam_dir = mk3(p.sin_x[x], p.sin_y[y], fmul(p.cos_x[x], p.cos_y[y]));  // scene.rs:213-222
+      const V3 pix_dir = matvec(to_world, cam_dir);
+      const size_t out_index = (size_t)y * p.width + x;
+      V3 acc = mk3(0.0, 0.0, 0.0);
+      uint32_t first = MISS_ID;
+      for (uint64_t s = 0; s < p.rays_per_pixel; ++s) {  // scene.rs:199-210
+        const double u0 = wy_f64(rng), u1 = wy_f64(rng), u2 = wy_f64(rng);
+        V3 pos = cam_pos + mk3(u0, u1, u2) * p.non_focal_offset;
+        const V3 focal = cam_pos + pix_dir * p.focal_length;
+        const double u3 = wy_f64(rng), u4 = wy_f64(rng), u5 = wy_f64(rng);
+        V3 dir = vnorm((focal + mk3(u3, u4, u5) * p.focal_offset) - pos);
+        V3 light = mk3(1.0, 1.0, 1.0), res = mk3(0.0, 0.0, 0.0);
+        ++n_paths;
+        if (sc.n_obj != 0) {  // scene.rs:223-242
+          for (uint64_t seg = 0; seg < p.max_bounces + 1ull; ++seg) {
+            if (light.x == 0.0 && light.y == 0.0 && light.z == 0.0) break;
+            const Hit h = USE_BVH ? closest_lbvh(sc, p.bvh, pos, dir, &n_panics, tc) : closest_brute(sc, pos, dir, &n_panics);
+            ++n_rays;
+            if (seg == 0 && s == 0) first = h.id;
+            if (h.id == MISS_ID) break;
+            ++n_hits;
+            pos = pos + dir * h.t;
+            const double* m = sc.mat + (size_t)h.id * MAT_STRIDE;
+            dir = random_bounce_dir(rng, dir, normal_at(sc, h.ref, pos), m[6]);  // scene.rs:275 — always drawn
+            res = res + light * mk3(m[3], m[4], m[5]);
+            light = light * mk3(m[0], m[1], m[2]);
+          }
+        }
+        acc = acc + res;
+      }
+      if (p.out_rgb) {
+        const V3 px = acc / (double)p.rays_per_pixel;
+        p.out_rgb[out_index * 3 + 0] = px.x, p.out_rgb[out_index * 3 + 1] = px.y, p.out_rgb[out_index * 3 + 2] = px.z;
+      }
+      if (p.out_ids) p.out_ids[out_index] = first;
+    }
+  }
+  if (p.ray_counter) {
+    unsigned long long r = n_rays, q = n_paths, e = n_panics, hh = n_hits;
+    unsigned long long nv = tc.nodes, pt = USE_BVH ? (unsigned long long)tc.prims : (unsigned long long)n_rays * sc.n_obj;
+    for (int o = 16; o > 0; o >>= 1) {
+      r += __shfl_down_sync(FULL, r, o), q += __shfl_down_sync(FULL, q, o), e += __shfl_down_sync(FULL, e, o);
+      hh += __shfl_down_sync(FULL, hh, o), nv += __shfl_down_sync(FULL, nv, o), pt += __shfl_down_sync(FULL, pt, o);
+    }
+    if ((threadIdx.x & 31u) == 0u) {
+      atomicAdd(&p.ray_counter[0], r), atomicAdd(&p.ray_counter[1], q), atomicAdd(&p.ray_counter[3], hh);
+      if (e) atomicAdd(&p.ray_counter[2], e);
+      if (nv) atomicAdd(&p.ray_counter[4], nv);
+      atomicAdd(&p.ray_counter[5], pt);
+    }
+  }
+}
+cudaError_t launch_render_rows(const RenderParams& p, cudaStream_t stream, uint32_t* out_launches) {
+  const unsigned grid = (p.height + 31u) / 32u;
+  if (p.use_bvh) render_rows_kernel<true><<<grid, 32, 0, stream>>>(p);
+  else render_rows_kernel<false><<<grid, 32, 0, stream>>>(p);
+  if (out_launches) *out_launches += 1;
+  return cudaGetLastError();
+}
+
 // Launch helper used by the API layer.  Returns the cudaError of the launch.
 cudaError_t launch_render(const RenderParams& p, int sm_count, cudaStream_t stream, uint32_t* out_launches) {
   if (!p.lane_kernel && pool_kernel_eligible(p)) return launch_render_pool(p, sm_count, stream, out_launches);

@@ -19,13 +19,13 @@ import numpy as np
 
 from . import _abi
 from ._abi import (MISS_ID, RTX_ACCEL_AUTO, RTX_ACCEL_BRUTE, RTX_ACCEL_LBVH, RTX_FLAG_LANE_KERNEL, RTX_FLAG_NO_RADIANCE,
-                   RTX_FLAG_PIXEL_QUEUE, RTX_FLAG_SAMPLE_QUEUE, RTX_FLAG_SHARD_IN_PLACE, RTX_FLAG_SHARD_ROWS, RTX_TILE, RtxError,
+                   RTX_FLAG_PIXEL_QUEUE, RTX_FLAG_SAMPLE_QUEUE, RTX_FLAG_SHARD_IN_PLACE, RTX_FLAG_SHARD_ROWS, RTX_FLAG_RNG_ROW, RTX_TILE, RtxError,
                    Shard, Stats)
 
 __all__ = ["Vector3", "Camera", "Config", "Material", "Sphere", "Plane", "Triangle", "Object", "Scene", "RtxError",
            "HostFrame", "MultiScene",
            "MISS_ID", "RTX_ACCEL_AUTO", "RTX_ACCEL_BRUTE", "RTX_ACCEL_LBVH", "RTX_FLAG_LANE_KERNEL", "RTX_FLAG_NO_RADIANCE",
-           "RTX_FLAG_PIXEL_QUEUE", "RTX_FLAG_SAMPLE_QUEUE", "RTX_FLAG_SHARD_IN_PLACE", "RTX_FLAG_SHARD_ROWS", "RTX_TILE",
+           "RTX_FLAG_PIXEL_QUEUE", "RTX_FLAG_SAMPLE_QUEUE", "RTX_FLAG_SHARD_IN_PLACE", "RTX_FLAG_SHARD_ROWS", "RTX_FLAG_RNG_ROW", "RTX_TILE",
            "device_count", "probe_fp64_peak", "shard_tile_count"]
 
 SHAPE_SPHERE, SHAPE_PLANE, SHAPE_TRIANGLE = 0, 1, 2

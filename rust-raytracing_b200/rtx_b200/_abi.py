@@ -78,6 +78,7 @@ RTX_FLAG_SHARD_IN_PLACE = 16
 RTX_FLAG_PIXEL_QUEUE = 32
 RTX_FLAG_SAMPLE_QUEUE = 64
 RTX_FLAG_SHARD_ROWS = 128
+RTX_FLAG_RNG_ROW = 256
 RTX_PEER_HANDLE_BYTES = 64
 RTX_TILE = 16
 RTX_NOALLOC_SCRATCH_BYTES = 32 << 20

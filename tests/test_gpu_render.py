@@ -441,3 +441,26 @@ def test_reference_panic_is_reported(rtx, oracle, gpu):
     ref = oracle.render_scene(sc, w, h, seed=3)
     assert ref["panics"] == st.triangle_panics
     assert rgb.tobytes() == clean.tobytes()  # the rejected triangle changes nothing
+
+
+def test_rng_row_mode_is_the_oracles_row_mode(rtx, oracle, gpu):
+    """RTX_FLAG_RNG_ROW: one CUDA thread per image row consuming one stream exactly as a reference row thread does
+    (scene.rs:149-161; every draw, also the bounce directions nothing traces).  Against the oracle's RNG_ROW mode:
+    hit ids and ray counts equal, radiance within the 1-spp gate (and bit-equal where no path bounced)."""
+    from rtx_b200 import scenes
+    for sc, flags, (w, h) in ((scenes.sphere_demo(rays_per_pixel=2, max_bounces=4), rtx.RTX_ACCEL_AUTO, (96, 54)),
+                              (scenes.sphere_demo(rays_per_pixel=1, max_bounces=0), rtx.RTX_ACCEL_AUTO, (33, 17)),
+                              (scenes.random_spheres(n=200, rays_per_pixel=1, max_bounces=3), rtx.RTX_ACCEL_LBVH, (48, 32))):
+        rgb, ids = sc.render(w, h, seed=7, flags=flags | rtx.RTX_FLAG_RNG_ROW, want_ids=True)
+        ref = oracle.render_scene(sc, w, h, seed=7, rng_mode=oracle.RNG_ROW)
+        assert np.array_equal(ids, ref["ids"])
+        assert sc.last_stats.rays == ref["rays"]
+        assert sc.last_stats.kernel_launches == 1 or flags == rtx.RTX_ACCEL_LBVH  # (+ the LBVH build's launches)
+        assert float(np.abs(rgb - ref["rgb"]).max()) <= TOL_1SPP
+        assert rgb.tobytes() == ref["rgb"].tobytes()  # the device sin/cos are glibc's bit for bit
+        # and it is NOT the default image (other seeding), while primary hit ids may differ only through jitter
+        assert sc.render(w, h, seed=7, flags=flags).tobytes() != rgb.tobytes() or sc.config.max_bounces == 0
+    with pytest.raises(rtx.RtxError):
+        import torch
+        t = torch.empty((17, 33, 3), dtype=torch.float64, device="cuda")
+        sc.render_device(33, 17, 1, rtx.RTX_FLAG_RNG_ROW, (0, 2), t.data_ptr(), None, None, 0)

@@ -69,6 +69,18 @@ def main():
         r = timed(sc, w, h, rtx_b200.RTX_ACCEL_LBVH, 2, 1)
         r.update(config="C3", scene="S2 10k spheres", width=w, height=h, spp=sc.config.rays_per_pixel)
         print(json.dumps(r), flush=True)
+    if "c3brute" in which:
+        # C3's scene as the reference's own O(N) scan (scene.rs:243-251): the 1.1 MB blob is beyond the 64 KB shared-memory
+        # stage, so the lane kernel reads it through L1/L2 with warp-uniform 128-bit loads
+        sc = scenes.random_spheres(n=10_000, rays_per_pixel=1, max_bounces=8)
+        w, h = 1920, 1080
+        r = timed(sc, w, h, rtx_b200.RTX_ACCEL_BRUTE, 2, 1)
+        r.update(config="C3 as brute force", scene="S2 10k spheres, scanned", width=w, height=h, spp=1,
+                 sphere_tests_per_s=r["prims_per_ray"] * r["rays"] / (r["ms_per_frame"] * 1e-3))
+        print(json.dumps(r), flush=True)
+        r2 = timed(sc, w, h, rtx_b200.RTX_ACCEL_LBVH, 2, 1)
+        r2.update(config="C3 same frame, LBVH", scene="S2 10k spheres", width=w, height=h, spp=1)
+        print(json.dumps(r2), flush=True)
     if "c4" in which:
         sc = scenes.terrain(grid=709, rays_per_pixel=1, max_bounces=4)
         w, h = (960, 540) if quick else (1920, 1080)
