@@ -263,36 +263,58 @@ __global__ void __launch_bounds__(PV_BLOCK) preview_kernel(const __grid_constant
     const F3 target_point = cam_pos + ray_dir * p.focal_length;
     F3 color = f3(0.0f, 0.0f, 0.0f);
     uint32_t first = MISS_ID;
-    for (uint32_t smp = 0; smp < p.rays_per_pixel; ++smp) {
-      const F3 ray_target = target_point + g.direction(tab) * p.focal_offset;
-      F3 pos = cam_pos + g.direction(tab) * p.non_focal_offset;
-      F3 dir = pnormalize(ray_target - pos);
-      // trace_ray, :151-169
-      F3 light = f3(1.0f, 1.0f, 1.0f), acc = f3(0.0f, 0.0f, 0.0f);
-      for (uint32_t b = 0; b < p.max_bounces; ++b) {
+    // fs_main's sample loop (:79-89) around trace_ray's bounce loop (:151-169), flattened into ONE loop whose trip is one
+    // closest_object call: a lane whose path has ended starts its pixel's next sample in the next trip instead of
+    // waiting at the inner loop's exit for the longest path of the warp (nested: 16.3 of 32 lanes per instruction).
+    // Per lane the operations and the RNG draws are the same, in the same order.
+    uint32_t smp = 0, b = 0;
+    bool fresh = true;
+    F3 pos = cam_pos, dir = ray_dir, light = f3(1.0f, 1.0f, 1.0f), acc = f3(0.0f, 0.0f, 0.0f);
+    while (smp < p.rays_per_pixel) {
+      if (fresh) {
+        const F3 ray_target = target_point + g.direction(tab) * p.focal_offset;
+        pos = cam_pos + g.direction(tab) * p.non_focal_offset;
+        dir = pnormalize(ray_target - pos);
+        light = f3(1.0f, 1.0f, 1.0f), acc = f3(0.0f, 0.0f, 0.0f);
+        b = 0;
+        fresh = false;
+      }
+      bool end = b >= p.max_bounces;
+      if (!end) {
         float dist;
         const uint32_t hit = pv_closest(sc, pos, dir, &dist);
         ++n_rays;
         if (smp == 0 && b == 0) first = hit;
-        if (hit == MISS_ID) break;
-        const float4 m0 = sc.f[PV_MAT0][hit], m1 = sc.f[PV_MAT1][hit];
-        pos = pos + dir * dist;
-        acc = acc + xyz(m1) * light;
-        light = light * xyz(m0);
-        if (light.x == 0.0f && light.y == 0.0f && light.z == 0.0f) break;
-        // calculate_normal: sphere.rs:78-80, plane.rs:78-80 (the RAW normal), triangle.rs:142-148
-        const uint32_t type = __float_as_uint(sc.f[PV_LO][hit].w);
-        F3 n;
-        if (type == 0u) n = pnormalize(pos - xyz(sc.f[PV_A][hit]));
-        else if (type == 1u) n = xyz(sc.f[PV_B][hit]);
-        else n = xyz(sc.f[PV_E][hit]);
-        // random_bounce, :170-183
-        const F3 rd = g.direction(tab);
-        const F3 refl = dir - (n * 2.0f) * pdot(dir, n);
-        const F3 fin = pnormalize(rd + (refl - rd) * pf_sub(1.0f, m0.w));
-        dir = pdot(fin, n) < 0.0f ? -fin : fin;
+        if (hit == MISS_ID) {
+          end = true;
+        } else {
+          const float4 m0 = sc.f[PV_MAT0][hit], m1 = sc.f[PV_MAT1][hit];
+          pos = pos + dir * dist;
+          acc = acc + xyz(m1) * light;
+          light = light * xyz(m0);
+          if (light.x == 0.0f && light.y == 0.0f && light.z == 0.0f) {
+            end = true;
+          } else {
+            // calculate_normal: sphere.rs:78-80, plane.rs:78-80 (the RAW normal), triangle.rs:142-148
+            const uint32_t type = __float_as_uint(sc.f[PV_LO][hit].w);
+            F3 n;
+            if (type == 0u) n = pnormalize(pos - xyz(sc.f[PV_A][hit]));
+            else if (type == 1u) n = xyz(sc.f[PV_B][hit]);
+            else n = xyz(sc.f[PV_E][hit]);
+            // random_bounce, :170-183 (drawn even when this was the last segment: the stream goes on into the next sample)
+            const F3 rd = g.direction(tab);
+            const F3 refl = dir - (n * 2.0f) * pdot(dir, n);
+            const F3 fin = pnormalize(rd + (refl - rd) * pf_sub(1.0f, m0.w));
+            dir = pdot(fin, n) < 0.0f ? -fin : fin;
+            ++b;
+          }
+        }
       }
-      color = color + acc;
+      if (end) {
+        color = color + acc;
+        ++smp;
+        fresh = true;
+      }
     }
     color = color / (float)p.rays_per_pixel;
     const size_t o = ((size_t)row * p.width + x) * 3;
