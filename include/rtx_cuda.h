@@ -251,6 +251,12 @@ rtx_status rtx_multi_add_triangles(rtx_multi* multi, const rtx_triangle* shapes,
 rtx_status rtx_multi_clear_objects(rtx_multi* multi);
 rtx_status rtx_multi_render(rtx_multi* multi, uint32_t width, uint32_t height, uint64_t seed, uint32_t flags,
                             double* out_rgb, uint32_t* out_primary_hit_id, rtx_stats* out_stats);
+/* RTX_FLAG_SHARD_ROWS arithmetic (pure host code): the strips of 4 pixel rows shard `index` of `count` owns (strip s
+ * belongs to shard s % count and is its local strip s / count), and the local strips of the band of tile rows
+ * [tile_row_first, tile_row_first + tile_row_count) = pixel rows [16 first, 16 (first + count)).               */
+uint64_t   rtx_shard_strip_count(uint32_t height, uint32_t index, uint32_t count);
+void       rtx_shard_band_strips(uint32_t height, uint32_t index, uint32_t count, uint32_t tile_row_first,
+                                 uint32_t tile_row_count, uint32_t* out_first_local_strip, uint32_t* out_strip_count);
 /* Number of tiles (and therefore compact-buffer slots) shard `index` of `count` owns. */
 uint64_t   rtx_shard_tile_count(uint32_t width, uint32_t height, uint32_t index, uint32_t count);
 /* The local tiles (first, count — indices into the shard's tile list, which is also the order of its compact

@@ -840,6 +840,14 @@ void rtx_shard_band_tiles(uint32_t width, uint32_t height, uint32_t index, uint3
 uint64_t rtx_shard_tile_count(uint32_t width, uint32_t height, uint32_t index, uint32_t count) {
   return shard_tiles(width, height, index, count);
 }
+uint64_t rtx_shard_strip_count(uint32_t height, uint32_t index, uint32_t count) { return shard_strips(height, index, count); }
+void rtx_shard_band_strips(uint32_t height, uint32_t index, uint32_t count, uint32_t tile_row_first, uint32_t tile_row_count,
+                           uint32_t* out_first_local_strip, uint32_t* out_strip_count) {
+  uint32_t first = 0, n = 0;
+  shard_band_strips(height, index, count, tile_row_first, tile_row_count, &first, &n);
+  if (out_first_local_strip) *out_first_local_strip = first;
+  if (out_strip_count) *out_strip_count = n;
+}
 
 // ---- render --------------------------------------------------------------------------------------
 rtx_status rtx_scene_render_device(rtx_scene* s, uint32_t width, uint32_t height, uint64_t seed, uint32_t flags,

@@ -163,6 +163,13 @@ class Scene {
     check(rtx_scene_render_to_rgb8(h_, (uint32_t)width, (uint32_t)height, seed, RTX_ACCEL_AUTO, out.data(), nullptr), h_);
     return out;
   }
+  // ≙ gpu::Scene::render (raytracing/gpu/scene.rs:26-52): the wgpu backend's f32 image (base_shader.wgsl), row 0 = bottom
+  std::vector<float> render_preview(size_t width, size_t height) {
+    sync();
+    std::vector<float> out(width * height * 3);
+    check(rtx_scene_render_preview_f32(h_, (uint32_t)width, (uint32_t)height, out.data(), nullptr, nullptr), h_);
+    return out;
+  }
   Config config;  // pub fields (scene.rs:80-84): edits take effect at the next render
   Camera camera;
   rtx_scene* handle() { return h_; }
@@ -174,6 +181,45 @@ class Scene {
     check(rtx_scene_set_camera(h_, &camera.c()), h_);
   }
   rtx_scene* h_ = nullptr;
+};
+
+// Scene over every listed GPU of this process (rtx_multi_*): same verbs, render() blocks and returns the whole image;
+// byte-identical to the one-GPU image.  ≙ raytracing/scene.rs:112-170.
+class MultiScene {
+ public:
+  MultiScene(Config config, Camera camera, const std::vector<int32_t>& devices) : config(config), camera(camera) {
+    rtx_config cc = config.c();
+    check(rtx_multi_create(&camera.c(), &cc, devices.data(), (uint32_t)devices.size(), &h_));
+  }
+  ~MultiScene() { rtx_multi_destroy(h_); }
+  MultiScene(const MultiScene&) = delete;
+  MultiScene& operator=(const MultiScene&) = delete;
+  void add_object(const object::Object& o) {
+    rtx_material m = o.material.c();
+    if (auto* s = std::get_if<object::Sphere>(&o.shape)) {
+      rtx_sphere c{s->position.c(), s->radius};
+      check(rtx_multi_add_spheres(h_, &c, &m, 1));
+    } else if (auto* p = std::get_if<object::Plane>(&o.shape)) {
+      rtx_plane c{p->position.c(), p->normal.c()};
+      check(rtx_multi_add_planes(h_, &c, &m, 1));
+    } else {
+      const auto& t = std::get<object::Triangle>(o.shape);
+      rtx_triangle c{{t.vertices[0].c(), t.vertices[1].c(), t.vertices[2].c()}};
+      check(rtx_multi_add_triangles(h_, &c, &m, 1));
+    }
+  }
+  // rgb: double[height][width][3], row 0 = bottom (pinned memory from rtx_host_alloc makes the per-GPU copies DMA)
+  void render(size_t width, size_t height, uint64_t seed, double* rgb, rtx_stats* stats = nullptr) {
+    rtx_config cc = config.c();
+    check(rtx_multi_set_camera(h_, &camera.c()));
+    check(rtx_multi_set_config(h_, &cc));
+    check(rtx_multi_render(h_, (uint32_t)width, (uint32_t)height, seed, RTX_ACCEL_AUTO, rgb, nullptr, stats));
+  }
+  Config config;
+  Camera camera;
+
+ private:
+  rtx_multi* h_ = nullptr;
 };
 
 }  // namespace rtx

@@ -99,6 +99,34 @@ int main() {
     threw = true;
   }
   EXPECT(threw);
+  {  // the same scene over every GPU of the process behind one handle (rtx_multi_*): the one-GPU image, bit for bit
+    std::vector<int32_t> devices;
+    for (int32_t d = 0; d < rtx_device_count() && d < 8; ++d) devices.push_back(d);
+    MultiScene multi(Config{}.with_rays_per_pixel(4).with_max_bounces(8), Camera({0, 0, 1}, {1, 0, 0}, deg90), devices);
+    multi.add_object({Plane{{0, 0, 0}, {0, 0, 1}}, Material::make({0.8, 0.8, 0.8}, {0, 0, 0}, 1.0)});
+    multi.add_object({Sphere{{6, 0, 1}, 1}, Material::make({0.9, 0.2, 0.2}, {0, 0, 0}, 1.0)});
+    multi.add_object({Sphere{{6, -2.5, 1}, 1}, Material::make({0.9, 0.9, 0.9}, {0, 0, 0}, 0.05)});
+    multi.add_object({Sphere{{6, 2.5, 1}, 1}, Material::make({0.2, 0.9, 0.2}, {0, 0, 0}, 0.5)});
+    multi.add_object({Sphere{{4, 1.2, 0.4}, 0.4}, Material::make({0.2, 0.3, 0.9}, {0, 0, 0}, 1.0)});
+    multi.add_object({Sphere{{4, -1.2, 0.4}, 0.4}, Material::light({2, 1.6, 1})});
+    multi.add_object({Sphere{{5, 0, 12}, 6}, Material::light({4, 4, 4})});
+    std::vector<double> buf(320 * 200 * 3);
+    rtx_stats ms{};
+    multi.render(320, 200, 1, buf.data(), &ms);
+    for (size_t y = 0; y < 200; ++y)
+      for (size_t x = 0; x < 320; ++x) {
+        const double* p = &buf[(y * 320 + x) * 3];
+        EXPECT(p[0] == img[y][x].x && p[1] == img[y][x].y && p[2] == img[y][x].z);
+      }
+    EXPECT(ms.rays == st.rays && ms.pixels == 320u * 200);
+    std::printf("multi ok: %zu device(s)\n", devices.size());
+  }
+  {  // the wgpu backend's f32 image of the same scene (rtx_scene_render_preview_f32)
+    auto pv = scene.render_preview(160, 100);
+    double s32 = 0;
+    for (float v : pv) s32 += v;
+    EXPECT(pv.size() == 160u * 100 * 3 && std::isfinite(s32) && s32 > 0);
+  }
   std::printf("render ok: %llu rays, %.3f ms device, mean radiance %.5f\nALL OK\n", (unsigned long long)st.rays,
               st.device_ms, sum / (320.0 * 200 * 3));
   return 0;

@@ -137,6 +137,8 @@ SIGNATURES = {
     "rtx_multi_render": (C.c_int32, [_vp, C.c_uint32, C.c_uint32, C.c_uint64, C.c_uint32, _vp, _vp, _P(Stats)]),
     "rtx_shard_band_tiles": (None, [C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32,
                                     _P(C.c_uint32), _P(C.c_uint32)]),
+    "rtx_shard_strip_count": (C.c_uint64, [C.c_uint32, C.c_uint32, C.c_uint32]),
+    "rtx_shard_band_strips": (None, [C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, _P(C.c_uint32), _P(C.c_uint32)]),
     "rtx_shard_tile_count": (C.c_uint64, [C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32]),
     "rtx_deinterleave_tiles": (C.c_int32, [C.c_uint32, C.c_uint32, C.c_uint32, _vp, _vp, _vp, _vp, _vp]),
     "rtx_scene_render_to_rgb8": (C.c_int32, [_vp, C.c_uint32, C.c_uint32, C.c_uint64, C.c_uint32, _vp, _P(Stats)]),

@@ -142,3 +142,59 @@ def test_band_tiles_match_enumeration():
                         got += n
                     assert got == len(mine)
     assert band(64, 64, 3, 2, 0, 4) == (0, 0) and band(64, 64, 0, 0, 0, 4) == (0, 0)  # invalid shards: nothing
+
+
+def test_row_strips_match_enumeration_and_compose_the_oracle_image():
+    """RTX_FLAG_SHARD_ROWS arithmetic (rtx_shard_strip_count / rtx_shard_band_strips, host only): strip s of 4 pixel rows
+    belongs to shard s % count as its local strip s // count; a band of tile rows is a contiguous range of local strips.
+    Against plain enumeration; and the rows the shards own, cut from an oracle image and put back strip by strip exactly
+    as rtx_scene_render_rows_to_host's 2-D copies place them (row = strip, pitch = count strips, ragged last strip
+    apart), give the image."""
+    import ctypes as C
+    sys.path.insert(0, os.path.join(ROOT, "rust-raytracing_b200"))
+    sys.path.insert(0, ROOT)
+    from oracle import oracle
+    from rtx_b200 import _abi, scenes
+    lib = _abi.load()
+
+    def band(h, r, n, r0, cnt):
+        a, b = C.c_uint32(123), C.c_uint32(456)
+        lib.rtx_shard_band_strips(h, r, n, r0, cnt, C.byref(a), C.byref(b))
+        return a.value, b.value
+
+    for h in (1, 3, 4, 5, 40, 131, 1080):
+        strips, ty = (h + 3) // 4, (h + T - 1) // T
+        for world in (1, 2, 3, 8):
+            owned = []
+            for r in range(world):
+                mine = list(range(r, strips, world))
+                assert lib.rtx_shard_strip_count(h, r, world) == len(mine)
+                owned += mine
+                for (r0, cnt) in ((0, ty), (0, 1), (1, 2), (ty - 1, 1), (ty - 1, 5), (ty, 3), (2, 0), (0, 10**6)):
+                    lo, hi = min(r0 * 4, strips), min((r0 + cnt) * 4, strips)
+                    want = [k for k, s_ in enumerate(mine) if lo <= s_ < hi]
+                    first, n = band(h, r, world, r0, cnt)
+                    assert n == len(want), (h, world, r, r0, cnt)
+                    if n:
+                        assert first == want[0]
+            assert sorted(owned) == list(range(strips))
+            assert lib.rtx_shard_strip_count(h, world, world) == 0  # index out of range
+    sc = scenes.sphere_demo(rays_per_pixel=1, max_bounces=1)
+    w, h = 40, 27  # ragged: 6 full strips + one of 3 rows
+    img = oracle.render_scene(sc, w, h, seed=2, nthreads=2)["rgb"]
+    strips = (h + 3) // 4
+    for world in (2, 3):
+        out = np.full_like(img, -1.0)
+        flat_src, flat_dst = img.reshape(-1), out.reshape(-1)
+        se = 4 * w * 3  # doubles per full strip
+        for r in range(world):
+            first, n = band(h, r, world, 0, 10**6)
+            g0, g_last = first * world + r, (first + n - 1) * world + r
+            ragged = g_last == strips - 1 and h % 4 != 0
+            for j in range(n - 1 if ragged else n):  # the 2-D copy: row j at pitch world * se
+                o = (g0 + j * world) * se
+                flat_dst[o:o + se] = flat_src[o:o + se]
+            if ragged:
+                o = g_last * se
+                flat_dst[o:] = flat_src[o:]
+        assert out.tobytes() == img.tobytes(), world

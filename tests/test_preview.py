@@ -146,3 +146,14 @@ def test_preview_device_variant(rtx, oracle, gpu):
     torch.cuda.synchronize(dev)
     ref = oracle.render_preview_scene(sc, w, h)
     assert out.cpu().numpy().tobytes() == ref["rgb"].tobytes() and int(cnt[0].item()) == ref["rays"]
+
+
+@pytest.mark.gpu
+def test_preview_kernel_reproduces_golden_fixture(rtx, gpu):
+    """The committed fixture (tests/golden/, generated from wgsl_oracle.cpp by make_golden.py), not a live oracle run."""
+    import os
+    from rtx_b200 import scenes
+    g = np.load(os.path.join(os.path.dirname(__file__), "golden", "preview_sphere_demo_96x64_2spp.npz"))
+    sc = scenes.sphere_demo(rays_per_pixel=2, max_bounces=5)
+    rgb, ids = sc.render_preview(96, 64, want_ids=True)
+    assert rgb.tobytes() == g["rgb"].tobytes() and np.array_equal(ids, g["ids"]) and sc.last_stats.rays == int(g["rays"])
