@@ -37,6 +37,7 @@ struct rtx_scene {
 
   // LBVH: [0] 3-D tree (spheres + triangles), [1..3] prism trees per dropped axis (rtx_lbvh.cuh)
   rtx::WideNode* d_bvh[4] = {nullptr, nullptr, nullptr, nullptr};
+  float4* d_bvh_aux[4] = {nullptr, nullptr, nullptr, nullptr};  // prism trees: per-child plane-gradient bounds (rtx_lbvh.cuh)
   uint32_t bvh_root[4] = {0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu};
   uint32_t bvh_count[4] = {0, 0, 0, 0};
   uint32_t bvh_build_launches = 0;
@@ -51,8 +52,6 @@ struct rtx_scene {
     uint32_t *d_prims = nullptr, *d_vals = nullptr, *d_left = nullptr, *d_right = nullptr, *d_parent = nullptr;
     uint8_t* d_valid = nullptr;
   } topo[4];
-  float prism_s[4] = {1, 1, 1, 1}, prism_z[4] = {0, 0, 0, 0};  // per prism tree: normal bounds (rtx_lbvh.cuh)
-  int prism_sign[4] = {0, 0, 0, 0};
   double* d_tri_raw = nullptr;  // device copy of tri_raw (boxes are computed from the vertices)
   size_t d_tri_raw_cap = 0;
 

@@ -44,7 +44,8 @@ __device__ __forceinline__ void atomic_max_f64(double* addr, double v) {
 // bounds[0..2] = min, [3..5] = max over the finite box corners (used for Morton quantisation and padding).
 __global__ void k_prim_boxes(const double* __restrict__ sph /* cx cy cz r2 */, const double* __restrict__ tri_raw /* 9/tri */,
                              const uint32_t* __restrict__ prims, uint32_t n, int open_axis, double* __restrict__ lo,
-                             double* __restrict__ hi, uint8_t* __restrict__ valid, double* __restrict__ bounds) {
+                             double* __restrict__ hi, uint8_t* __restrict__ valid, double* __restrict__ bounds,
+                             double* __restrict__ grad /* prism trees: [n][2] plane gradient (d a/d b, d a/d c); else null */) {
   const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
   const uint32_t ref = prims[i], idx = ref & REF_INDEX_MASK;
@@ -75,6 +76,20 @@ __global__ void k_prim_boxes(const double* __restrict__ sph /* cx cy cz r2 */, c
     // test (the reported point of a phantom hit may be anywhere along it) but uses it for its |t| bounds
   }
   for (int k = 0; k < 3; ++k) lo[(size_t)i * 3 + k] = l[k], hi[(size_t)i * 3 + k] = h[k];
+  if (grad) {
+    // the triangle's plane as a height function along the dropped axis a over the kept axes b, c:
+    // gradient = -(n_b, n_c) / n_a with n = cross(v1 - v0, v2 - v0) (triangle.rs:104-107 up to normalisation).
+    // A plane parallel to a (n_a = 0) or non-finite data: NaN here = "no bound" (k_refit turns it into +-inf).
+    double gb = CUDART_NAN, gc = CUDART_NAN;
+    if (ok && open_axis < 3 && (ref & ~REF_INDEX_MASK) == REF_TRIANGLE) {
+      const double* v = tri_raw + (size_t)idx * 9;
+      const double r[3] = {v[3] - v[0], v[4] - v[1], v[5] - v[2]}, s[3] = {v[6] - v[0], v[7] - v[1], v[8] - v[2]};
+      const double nrm[3] = {r[1] * s[2] - r[2] * s[1], r[2] * s[0] - r[0] * s[2], r[0] * s[1] - r[1] * s[0]};
+      const int a = open_axis, b = (a + 1) % 3, c = (a + 2) % 3;
+      if (nrm[a] != 0.0) gb = -nrm[b] / nrm[a], gc = -nrm[c] / nrm[a];
+    }
+    grad[(size_t)i * 2 + 0] = gb, grad[(size_t)i * 2 + 1] = gc;
+  }
 }
 
 // ---- 2. Morton keys -----------------------------------------------------------------------------------------
@@ -240,7 +255,7 @@ __global__ void k_refit(const uint32_t* __restrict__ sorted_vals, const uint32_t
                         const double* __restrict__ lo, const double* __restrict__ hi, int m,
                         const double* __restrict__ bounds, const uint32_t* __restrict__ left,
                         const uint32_t* __restrict__ right, const uint32_t* __restrict__ parent,
-                        uint32_t* __restrict__ flags, BvhNode* __restrict__ nodes) {
+                        uint32_t* __restrict__ flags, BvhNode* __restrict__ nodes, const double* __restrict__ grad) {
   const int j = blockIdx.x * blockDim.x + threadIdx.x;
   if (j >= m) return;
   const double pad = box_pad(bounds);
@@ -250,6 +265,12 @@ __global__ void k_refit(const uint32_t* __restrict__ sorted_vals, const uint32_t
   for (int k = 0; k < 3; ++k) {
     nd.lo[k] = lo[(size_t)src * 3 + k] - pad;  // -inf - pad = -inf for opened axes
     nd.hi[k] = hi[(size_t)src * 3 + k] + pad;
+  }
+  for (int k = 0; k < 2; ++k) {
+    const double g = grad ? grad[(size_t)src * 2 + k] : 0.0;
+    const bool fin = g - g == 0.0;
+    nd.glo[k] = fin ? g : -CUDART_INF;
+    nd.ghi[k] = fin ? g : CUDART_INF;
   }
   nd.left = BVH_END;
   nd.escape = BVH_END;
@@ -269,6 +290,10 @@ __global__ void k_refit(const uint32_t* __restrict__ sorted_vals, const uint32_t
       p.lo[k] = fmin(a->lo[k], b->lo[k]);
       p.hi[k] = fmax(a->hi[k], b->hi[k]);
     }
+    for (int k = 0; k < 2; ++k) {
+      p.glo[k] = fmin(a->glo[k], b->glo[k]);
+      p.ghi[k] = fmax(a->ghi[k], b->ghi[k]);
+    }
     p.left = left[cur];
     p.escape = BVH_END;
     p.prim = BVH_NO_PRIM;
@@ -285,8 +310,19 @@ __device__ __forceinline__ uint32_t child_ref(const BvhNode* __restrict__ nodes,
   if (prim == BVH_NO_PRIM) return c;  // internal node index (< m-1 < 2^30)
   return WIDE_LEAF | (((prim & ~REF_INDEX_MASK) == REF_TRIANGLE) ? WIDE_TRI : 0u) | (prim & REF_INDEX_MASK);
 }
+// gradient bounds of a child, f32, rounded outward and widened by 1e-6 relative (they are compared with quantities
+// derived from the runtime's own normal, which agrees with this one to ~1e-16)
+__device__ __forceinline__ float4 child_gradient(const BvhNode* __restrict__ nodes, uint32_t c) {
+  float v[4];
+  for (int k = 0; k < 2; ++k) {
+    const double lo = nodes[c].glo[k], hi = nodes[c].ghi[k];
+    v[2 * k + 0] = __double2float_rd(lo - fabs(lo) * 1e-6 - 1e-30);
+    v[2 * k + 1] = __double2float_ru(hi + fabs(hi) * 1e-6 + 1e-30);
+  }
+  return make_float4(v[0], v[1], v[2], v[3]);
+}
 __global__ void k_emit_wide(int m, const BvhNode* __restrict__ nodes, const uint32_t* __restrict__ left,
-                            const uint32_t* __restrict__ right, WideNode* __restrict__ out) {
+                            const uint32_t* __restrict__ right, WideNode* __restrict__ out, float4* __restrict__ aux) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (m == 1) {  // a single leaf: root = one wide node with an empty second slot
     if (i != 0) return;
@@ -301,6 +337,7 @@ __global__ void k_emit_wide(int m, const BvhNode* __restrict__ nodes, const uint
     w.c1 = w.c0;
     w.pad[0] = w.pad[1] = 0;
     out[0] = w;
+    if (aux) aux[0] = aux[1] = child_gradient(nodes, 0);
     return;
   }
   if (i >= m - 1) return;
@@ -316,6 +353,7 @@ __global__ void k_emit_wide(int m, const BvhNode* __restrict__ nodes, const uint
   w.c1 = child_ref(nodes, r);
   w.pad[0] = w.pad[1] = 0;
   out[i] = w;
+  if (aux) aux[2 * i] = child_gradient(nodes, l), aux[2 * i + 1] = child_gradient(nodes, r);
 }
 
 __global__ void k_count_valid(const uint64_t* __restrict__ sorted_keys, uint32_t n, uint32_t* __restrict__ out) {
@@ -360,8 +398,9 @@ static void free_topo(rtx_scene::TreeTopo& t) {
 
 static rtx_status build_tree(rtx_scene* s, const std::vector<uint32_t>& prims, int open_axis, const double* d_tri_raw,
                              cudaStream_t stream, WideNode** out_nodes, uint32_t* out_root, uint32_t* out_count,
-                             uint32_t* launches, rtx_scene::TreeTopo* topo) {
+                             uint32_t* launches, rtx_scene::TreeTopo* topo, float4** out_aux) {
   *out_nodes = nullptr;
+  *out_aux = nullptr;
   *out_root = BVH_END;
   *out_count = 0;
   free_topo(*topo);
@@ -370,9 +409,11 @@ static rtx_status build_tree(rtx_scene* s, const std::vector<uint32_t>& prims, i
   if (n == 0) return RTX_OK;
   const unsigned B = 256, G = (n + B - 1) / B;
   Tmp<uint32_t> d_prims, d_vals[2], d_hist, d_left, d_right, d_parent, d_flags, d_m;
-  Tmp<double> d_lo, d_hi, d_bounds;
+  Tmp<double> d_lo, d_hi, d_bounds, d_grad;
   Tmp<uint8_t> d_valid;
   Tmp<uint64_t> d_keys[2];
+  const bool prism = open_axis < 3;
+  if (prism) LBVH_TRY(d_grad.alloc((size_t)n * 2));
   LBVH_TRY(d_prims.alloc(n));
   LBVH_TRY(d_lo.alloc((size_t)n * 3));
   LBVH_TRY(d_hi.alloc((size_t)n * 3));
@@ -388,7 +429,8 @@ static rtx_status build_tree(rtx_scene* s, const std::vector<uint32_t>& prims, i
   const double b0[6] = {inf, inf, inf, -inf, -inf, -inf};
   LBVH_TRY(cudaMemcpyAsync(d_bounds.p, b0, sizeof(b0), cudaMemcpyHostToDevice, stream));
   const double* d_sph = reinterpret_cast<const double*>(s->d_blob + s->layout.off_sph);
-  k_prim_boxes<<<G, B, 0, stream>>>(d_sph, d_tri_raw, d_prims.p, n, open_axis, d_lo.p, d_hi.p, d_valid.p, d_bounds.p);
+  k_prim_boxes<<<G, B, 0, stream>>>(d_sph, d_tri_raw, d_prims.p, n, open_axis, d_lo.p, d_hi.p, d_valid.p, d_bounds.p,
+                                    prism ? d_grad.p : nullptr);
   k_morton<<<G, B, 0, stream>>>(d_lo.p, d_hi.p, d_valid.p, n, open_axis, d_bounds.p, d_keys[0].p, d_vals[0].p);
   *launches += 2;
   // radix sort: 8 passes x 8 bits
@@ -417,10 +459,13 @@ static rtx_status build_tree(rtx_scene* s, const std::vector<uint32_t>& prims, i
   WideNode* wide = nullptr;
   const uint32_t n_wide = m > 1 ? m - 1 : 1;
   LBVH_TRY(cudaMalloc((void**)&nodes, (size_t)total * sizeof(BvhNode)));
+  float4* aux = nullptr;
   {
     cudaError_t ew = cudaMalloc((void**)&wide, (size_t)n_wide * sizeof(WideNode));
+    if (ew == cudaSuccess && prism) ew = cudaMalloc((void**)&aux, (size_t)n_wide * 2 * sizeof(float4));
     if (ew != cudaSuccess) {
       cudaFree(nodes);
+      cudaFree(wide);
       return cuda_fail(s, ew, "lbvh wide nodes");
     }
   }
@@ -437,8 +482,8 @@ static rtx_status build_tree(rtx_scene* s, const std::vector<uint32_t>& prims, i
     const unsigned Gm = (m + B - 1) / B;
     if (m > 1) k_hierarchy<<<Gm, B, 0, stream>>>(d_keys[cur].p, (int)m, d_left.p, d_right.p, d_parent.p);
     k_refit<<<Gm, B, 0, stream>>>(d_vals[cur].p, d_prims.p, d_lo.p, d_hi.p, (int)m, d_bounds.p, d_left.p, d_right.p,
-                                  d_parent.p, d_flags.p, nodes);
-    k_emit_wide<<<Gm, B, 0, stream>>>((int)m, nodes, d_left.p, d_right.p, wide);
+                                  d_parent.p, d_flags.p, nodes, prism ? d_grad.p : nullptr);
+    k_emit_wide<<<Gm, B, 0, stream>>>((int)m, nodes, d_left.p, d_right.p, wide, aux);
     *launches += 3;
     if ((e = cudaGetLastError()) != cudaSuccess || (e = cudaStreamSynchronize(stream)) != cudaSuccess) {
       st = cuda_fail(s, e, "lbvh build kernels");
@@ -448,8 +493,10 @@ static rtx_status build_tree(rtx_scene* s, const std::vector<uint32_t>& prims, i
   cudaFree(nodes);
   if (st != RTX_OK) {
     cudaFree(wide);
+    cudaFree(aux);
     return st;
   }
+  *out_aux = aux;
   *out_nodes = wide;
   *out_root = 0u;  // the root is wide node 0
   *out_count = n_wide;
@@ -467,14 +514,16 @@ static rtx_status build_tree(rtx_scene* s, const std::vector<uint32_t>& prims, i
 // Same hierarchy, new boxes: recompute the primitive boxes from the (updated) scene, check that the same
 // primitives are inside the tree, then redo the bottom-up pass and the traversal nodes in place.
 // *needs_rebuild is set when membership changed.  Synchronous on `stream`.
-static rtx_status refit_tree(rtx_scene* s, const rtx_scene::TreeTopo& t, WideNode* wide, cudaStream_t stream,
+static rtx_status refit_tree(rtx_scene* s, const rtx_scene::TreeTopo& t, WideNode* wide, float4* aux, cudaStream_t stream,
                              bool* needs_rebuild, uint32_t* launches) {
   if (t.n == 0 || t.m == 0) return RTX_OK;
   const unsigned B = 256, G = (t.n + B - 1) / B, Gm = (t.m + B - 1) / B;
-  Tmp<double> d_lo, d_hi, d_bounds;
+  Tmp<double> d_lo, d_hi, d_bounds, d_grad;
   Tmp<uint8_t> d_valid;
   Tmp<uint32_t> d_flags, d_diff;
   Tmp<BvhNode> d_nodes;
+  const bool prism = t.open_axis < 3 && aux;
+  if (prism) LBVH_TRY(d_grad.alloc((size_t)t.n * 2));
   LBVH_TRY(d_lo.alloc((size_t)t.n * 3));
   LBVH_TRY(d_hi.alloc((size_t)t.n * 3));
   LBVH_TRY(d_valid.alloc(t.n));
@@ -488,7 +537,8 @@ static rtx_status refit_tree(rtx_scene* s, const rtx_scene::TreeTopo& t, WideNod
   LBVH_TRY(cudaMemsetAsync(d_diff.p, 0, 4, stream));
   LBVH_TRY(cudaMemsetAsync(d_flags.p, 0, (size_t)t.m * 4, stream));
   const double* d_sph = reinterpret_cast<const double*>(s->d_blob + s->layout.off_sph);
-  k_prim_boxes<<<G, B, 0, stream>>>(d_sph, s->d_tri_raw, t.d_prims, t.n, t.open_axis, d_lo.p, d_hi.p, d_valid.p, d_bounds.p);
+  k_prim_boxes<<<G, B, 0, stream>>>(d_sph, s->d_tri_raw, t.d_prims, t.n, t.open_axis, d_lo.p, d_hi.p, d_valid.p, d_bounds.p,
+                                    prism ? d_grad.p : nullptr);
   k_valid_diff<<<G, B, 0, stream>>>(d_valid.p, t.d_valid, t.n, d_diff.p);
   uint32_t diff = 0;
   LBVH_TRY(cudaMemcpyAsync(&diff, d_diff.p, 4, cudaMemcpyDeviceToHost, stream));
@@ -499,8 +549,8 @@ static rtx_status refit_tree(rtx_scene* s, const rtx_scene::TreeTopo& t, WideNod
     return RTX_OK;
   }
   k_refit<<<Gm, B, 0, stream>>>(t.d_vals, t.d_prims, d_lo.p, d_hi.p, (int)t.m, d_bounds.p, t.d_left, t.d_right, t.d_parent,
-                                d_flags.p, d_nodes.p);
-  k_emit_wide<<<Gm, B, 0, stream>>>((int)t.m, d_nodes.p, t.d_left, t.d_right, wide);
+                                d_flags.p, d_nodes.p, prism ? d_grad.p : nullptr);
+  k_emit_wide<<<Gm, B, 0, stream>>>((int)t.m, d_nodes.p, t.d_left, t.d_right, wide, prism ? aux : nullptr);
   *launches += 2;
   LBVH_TRY(cudaGetLastError());
   LBVH_TRY(cudaStreamSynchronize(stream));
@@ -510,7 +560,9 @@ static rtx_status refit_tree(rtx_scene* s, const rtx_scene::TreeTopo& t, WideNod
 void free_lbvh(rtx_scene* s) {
   for (int k = 0; k < 4; ++k) {
     if (s->d_bvh[k]) cudaFree(s->d_bvh[k]);
+    if (s->d_bvh_aux[k]) cudaFree(s->d_bvh_aux[k]);
     s->d_bvh[k] = nullptr;
+    s->d_bvh_aux[k] = nullptr;
     s->bvh_root[k] = BVH_END;
     s->bvh_count[k] = 0;
     free_topo(s->topo[k]);
@@ -519,46 +571,11 @@ void free_lbvh(rtx_scene* s) {
   s->bvh_refit = false;
 }
 
-// S, Z and the sign flag of every prism tree (rtx_lbvh.cuh), from the packed triangle records: n = rec[3..5] is the
-// unit normal the distance function uses, the pivots say which axis contains() drops.
-static void compute_prism_constants(rtx_scene* s) {
-  double smax[3] = {0, 0, 0}, zmin[3] = {1, 1, 1};
-  bool pos[3] = {false, false, false}, neg[3] = {false, false, false}, any[3] = {false, false, false};
-  const size_t n_tri = s->tri_id.size();
-  for (size_t i = 0; i < n_tri; ++i) {
-    const double* rec = &s->tri[i * TRI_STRIDE];
-    uint64_t code;
-    std::memcpy(&code, &rec[13], 8);
-    if (code & (TRI_DEGENERATE | TRI_PANIC)) continue;
-    const int i1 = (int)((code >> TRI_I1_SHIFT) & 3), i2 = (int)((code >> TRI_I2_SHIFT) & 3), a = 3 - i1 - i2;
-    const double na = rec[3 + a], nb = rec[3 + (a + 1) % 3], nc = rec[3 + (a + 2) % 3];
-    any[a] = true;
-    if (!(na - na == 0.0) || !(nb - nb == 0.0) || !(nc - nc == 0.0)) {  // non-finite normal: no bound holds
-      smax[a] = std::numeric_limits<double>::infinity();
-      zmin[a] = 0.0;
-      pos[a] = neg[a] = true;
-      continue;
-    }
-    smax[a] = std::fmax(smax[a], std::sqrt(nb * nb + nc * nc));
-    zmin[a] = std::fmin(zmin[a], std::fabs(na));
-    (na > 0.0 ? pos[a] : neg[a]) = true;  // n_a == 0 counts as "mixed" through zmin = 0 anyway
-  }
-  for (int a = 0; a < 3; ++a) {
-    const float sf = (float)(smax[a] * 1.000001), zf = (float)(zmin[a] * 0.999999);
-    s->prism_s[1 + a] = any[a] ? std::nextafterf(sf, std::numeric_limits<float>::infinity()) : 1.0f;
-    s->prism_z[1 + a] = any[a] ? std::fmax(0.0f, std::nextafterf(zf, 0.0f)) : 0.0f;
-    s->prism_sign[1 + a] = (pos[a] && !neg[a]) ? 1 : ((neg[a] && !pos[a]) ? -1 : 0);
-  }
-  s->prism_s[0] = 1.0f, s->prism_z[0] = 0.0f, s->prism_sign[0] = 0;
-}
-
 void fill_bvh_view(const rtx_scene* s, bool use_bvh, BvhView* bv) {
   for (int k = 0; k < 4; ++k) {
     bv->nodes[k] = use_bvh ? s->d_bvh[k] : nullptr;
+    bv->aux[k] = use_bvh ? s->d_bvh_aux[k] : nullptr;
     bv->root[k] = use_bvh ? s->bvh_root[k] : BVH_END;
-    bv->prism_s[k] = s->prism_s[k];
-    bv->prism_z[k] = s->prism_z[k];
-    bv->prism_sign[k] = s->prism_sign[k];
   }
 }
 
@@ -566,12 +583,11 @@ void fill_bvh_view(const rtx_scene* s, bool use_bvh, BvhView* bv) {
 // must be uploaded.  Rebuilt whenever the object list changed.
 rtx_status ensure_lbvh(rtx_scene* s, cudaStream_t stream) {
   if (s->bvh_valid && s->bvh_refit) {  // rtx_scene_update_*: primitives moved, hierarchy kept
-    compute_prism_constants(s);
     bool rebuild = false;
     uint32_t launches = 0;
     for (int k = 0; k < 4 && !rebuild; ++k) {
       if (s->bvh_root[k] == BVH_END) continue;
-      rtx_status st = refit_tree(s, s->topo[k], s->d_bvh[k], stream, &rebuild, &launches);
+      rtx_status st = refit_tree(s, s->topo[k], s->d_bvh[k], s->d_bvh_aux[k], stream, &rebuild, &launches);
       if (st != RTX_OK) return st;
     }
     s->bvh_refit = false;
@@ -595,7 +611,6 @@ rtx_status ensure_lbvh(rtx_scene* s, cudaStream_t stream) {
     const int i1 = (int)((code >> TRI_I1_SHIFT) & 3), i2 = (int)((code >> TRI_I2_SHIFT) & 3);
     prism[3 - i1 - i2].push_back(REF_TRIANGLE | i);  // the coordinate contains() never looks at
   }
-  compute_prism_constants(s);
   if (n_tri) {  // persistent: refits recompute boxes from it
     if (s->d_tri_raw_cap < s->tri_raw.size() * 8 || !s->d_tri_raw) {
       cudaFree(s->d_tri_raw);
@@ -607,10 +622,10 @@ rtx_status ensure_lbvh(rtx_scene* s, cudaStream_t stream) {
   }
   uint32_t launches = 0;
   rtx_status st = build_tree(s, all, 3, s->d_tri_raw, stream, &s->d_bvh[0], &s->bvh_root[0], &s->bvh_count[0], &launches,
-                             &s->topo[0]);
+                             &s->topo[0], &s->d_bvh_aux[0]);
   for (int a = 0; a < 3 && st == RTX_OK; ++a)
     st = build_tree(s, prism[a], a, s->d_tri_raw, stream, &s->d_bvh[1 + a], &s->bvh_root[1 + a], &s->bvh_count[1 + a],
-                    &launches, &s->topo[1 + a]);
+                    &launches, &s->topo[1 + a], &s->d_bvh_aux[1 + a]);
   if (st != RTX_OK) {
     free_lbvh(s);
     return st;

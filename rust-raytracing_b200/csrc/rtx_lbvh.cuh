@@ -17,16 +17,13 @@
 // the infinite prism over the triangle's projection along the coordinate contains() drops
 // (triangle.rs:96-100).  One "prism tree" per dropped axis a is traversed after the 3-D tree.  Its nodes keep
 // the triangles' true 3-D boxes, but a node is entered on the evidence of the two KEPT axes only (the reported
-// point may be anywhere along a), pruned by the best distance so far and by two bounds that hold for every
-// triangle T below the node (unit normal n, |n_perp| <= S, |n_a| >= Z; v0 inside the node's box):
-//  (A) "not a phantom": if the node lies wholly ahead of the origin along a (distance >= g > 0 in the direction
-//      the ray travels along a), g*Z > S*dperp_max and |d_a|*Z > |d_perp|*S, then for every T both n.(v0 - pos)
-//      and d.n take the sign of n_a (their a-terms dominate): the plane is in FRONT, the hit is an ordinary
-//      one and the 3-D tree finds it;
-//  (B) |t| = |n.(v0 - pos)| / |d.n| <= (S*dperp_max + da_max) / (|d_a|*Z - |d_perp|*S) =: U when the denominator
-//      is positive: the reported point lies at parameter <= U, so a node whose kept-axes entry parameter exceeds
-//      U cannot contain it.
-// Without them a ray that leaves a height field upwards walks the footprint of every triangle under its path.
+// point may be anywhere along a), pruned by the best distance so far and by the gradient bound of
+// prism_gradient_test below: per child, bounds of the plane gradients of the triangles under it turn "is there a
+// triangle here whose plane, cut BEHIND the origin, reports a point over this box?" into interval arithmetic.
+// (Round 1 had two tree-wide bounds instead — (A) "the node lies wholly ahead, so every plane is in front" and (B) an
+// upper bound of |t| from tree-wide normal bounds S, Z; the per-child gradient bound implies both and costs neither a
+// square root nor a division per child: C4 8.35 -> 4.47 ms.)  Without any such bound a ray that leaves a height field
+// upwards walks the footprint of every triangle under its path.
 #pragma once
 #include "rtx_trace.cuh"
 
@@ -35,9 +32,10 @@ namespace rtx {
 constexpr uint32_t BVH_END = 0xFFFFFFFFu;
 constexpr uint32_t BVH_NO_PRIM = 0xFFFFFFFFu;
 
-struct __align__(16) BvhNode {  // 64 B = four 128-bit loads
+struct __align__(16) BvhNode {  // f64 build node (build-time only)
   double lo[3];
   double hi[3];
+  double glo[2], ghi[2];  // prism trees: bounds of the plane gradients (d a / d b, d a / d c) of the triangles below
   uint32_t left;    // internal: first child (its sibling is reached through the child's escape)
   uint32_t escape;  // next node once this subtree is done (BVH_END at the end of the walk)
   uint32_t prim;    // leaf: REF_* | index ; internal: BVH_NO_PRIM
@@ -56,12 +54,10 @@ struct __align__(16) WideNode {  // 64 B = four 128-bit loads
 
 struct BvhView {
   const WideNode* nodes[4];  // [0] 3-D tree over spheres + triangles; [1..3] prism trees (dropped axis x,y,z)
+  // prism trees: per node two float4, one per child: (gb_lo, gb_hi, gc_lo, gc_hi) — outward-rounded bounds of the plane
+  // gradients g = -n_perp / n_a of the triangles below that child (bound (C) of box_test_prism); +-inf = no bound
+  const float4* aux[4];
   uint32_t root[4];          // BVH_END when the tree is empty, else 0
-  // Per prism tree (index 1 + a, a = dropped axis), over its triangles' unit normals n:
-  //   prism_s >= max |n without its a-component|, prism_z <= min |n_a|  (rounded outward),
-  //   prism_sign = +1 / -1 when every n_a has that sign, 0 when mixed.
-  float prism_s[4], prism_z[4];
-  int prism_sign[4];
 };
 
 #if defined(__CUDACC__)
@@ -111,10 +107,19 @@ RTX_D void slab(const float* lo, const float* hi, const RayF32& r, float& tn, fl
   tf = __fmaf_rn(xf, r.inv[K], r.cf[K]);
 }
 // visit unless provably empty, provably behind the origin, or provably beyond the best distance
-RTX_D bool slab_verdict(float tn, float tf, float best_up, float& tnear) {
+RTX_D bool slab_verdict(float tn, float tf, float best_up, float& tnear, float& tfar) {
   tnear = __fmaf_rn(-fabsf(tn), SLAB_REL, tn);
-  const float tfar = __fmaf_rn(fabsf(tf), SLAB_REL, tf);
+  tfar = __fmaf_rn(fabsf(tf), SLAB_REL, tf);
   return !(tfar < fmaxf(tnear, 0.0f)) && !(tnear > best_up);
+}
+RTX_D bool slab_verdict(float tn, float tf, float best_up, float& tnear) {
+  float tfar;
+  return slab_verdict(tn, tf, best_up, tnear, tfar);
+}
+// [a_lo, a_hi] * [b_lo, b_hi] with outward rounding (finite operands)
+RTX_D void imul(float a_lo, float a_hi, float b_lo, float b_hi, float& lo, float& hi) {
+  lo = fminf(fminf(__fmul_rd(a_lo, b_lo), __fmul_rd(a_lo, b_hi)), fminf(__fmul_rd(a_hi, b_lo), __fmul_rd(a_hi, b_hi)));
+  hi = fmaxf(fmaxf(__fmul_ru(a_lo, b_lo), __fmul_ru(a_lo, b_hi)), fmaxf(__fmul_ru(a_hi, b_lo), __fmul_ru(a_hi, b_hi)));
 }
 RTX_D bool box_test(const float* lo, const float* hi, const RayF32& r, float best_up, float& tnear) {
   float tn0, tf0, tn1, tf1, tn2, tf2;
@@ -124,51 +129,76 @@ RTX_D bool box_test(const float* lo, const float* hi, const RayF32& r, float bes
   return slab_verdict(fmaxf(fmaxf(tn0, tn1), tn2), fminf(fminf(tf0, tf1), tf2), best_up, tnear);
 }
 
-// Per-ray constants of the prism tree that drops axis A: rigorous f32 enclosures of the origin, and the lower
-// bound `den` of |d.n| over the tree's triangles: |d_a|*Z - |d_perp|*S (<= 0: no bound).
+// Per-ray constants of the prism walks: rigorous f32 enclosures of the origin and of the unit direction.
 struct PrismRay {
-  float o_dn[3], o_up[3];
-  float den, s, z;
+  float o_dn[3], o_up[3];  // enclosures of the origin
+  float d_dn[3], d_up[3];  // enclosures of the unit direction
 };
-template <int A>
-RTX_D PrismRay make_prism_ray(const BvhView& bv, V3 pos, V3 dn) {
-  constexpr int B = (A + 1) % 3, C = (A + 2) % 3;
+RTX_D PrismRay make_prism_ray(V3 pos, V3 dn) {
   PrismRay pr;
   const double p[3] = {pos.x, pos.y, pos.z}, d[3] = {dn.x, dn.y, dn.z};
 #pragma unroll
-  for (int k = 0; k < 3; ++k) pr.o_dn[k] = __double2float_rd(p[k]), pr.o_up[k] = __double2float_ru(p[k]);
-  pr.s = bv.prism_s[1 + A];
-  pr.z = bv.prism_z[1 + A];
-  const float da = __double2float_rd(fabs(d[A]) * 0.999999);
-  const float dp = __double2float_ru(sqrt(d[B] * d[B] + d[C] * d[C]) * 1.000001);
-  pr.den = __fsub_rd(__fmul_rd(da, pr.z), __fmul_ru(dp, pr.s));
+  for (int k = 0; k < 3; ++k) {
+    pr.o_dn[k] = __double2float_rd(p[k]), pr.o_up[k] = __double2float_ru(p[k]);
+    pr.d_dn[k] = __double2float_rd(d[k]), pr.d_up[k] = __double2float_ru(d[k]);
+  }
   return pr;
 }
-// Entry test of a node of the prism tree that drops axis A: slabs on the kept axes, then bounds (A) and (B)
-// above.  All roundings are directed so that a node is only skipped when the exact-arithmetic statement holds
-// with margin; the f64 quantities they bound (|t| as computed by triangle_distance, the reported point) differ
-// from the exact ones by ~1e-16 relative, far inside the 1e-6 margins and the 2^-20 box padding.
+// Entry test of a child of a node of the prism tree that drops axis A: slabs on the kept axes, then the gradient
+// bound.  All roundings are directed so that a child is only skipped when the exact-arithmetic statement holds with
+// margin; the f64 quantities they bound (|t| as computed by triangle_distance, the reported point) differ from the
+// exact ones by ~1e-16 relative, far inside the margins and the 2^-20 box padding.
+// The gradient bound.  Write a triangle's plane over the kept axes as a height function along
+// a with gradient g = -(n_b, n_c) / n_a.  Then n.(v0 - pos) = n_a * gap and d.n = n_a * slope, with
+//   gap   = (v0 - pos)_a - g.(v0 - pos)_perp     (how far the plane, extended to pos, lies above pos along a)
+//   slope = d_a - g.d_perp
+// so the quotient of triangle.rs:34 is t = gap / slope — n_a cancels — and a phantom hit needs t < 0 with the reported
+// point at parameter |t| over the node: |t| inside the kept-axes window [tnear, tfar] (and <= the best distance).
+// With v0 inside the child's box and g inside the child's gradient box, gap and slope are intervals; the child is
+// skipped when no (gap, slope) in them gives such a t.  All interval arithmetic is f32 with directed rounding on enclosures of
+// pos, d and the padded boxes; the f64 evaluation it brackets (triangle_distance) differs from exact arithmetic by
+// ~1e-14 absolute, the box padding alone is 2^-20 of the scene scale.
+template <int A>
+RTX_D bool prism_gradient_test(const float* lo, const float* hi, const PrismRay& pr, float4 g, float tnear, float tfar,
+                               float best_up) {
+  constexpr int B = (A + 1) % 3, C = (A + 2) % 3;
+  if (!(fabsf(g.x) < 1e30f && fabsf(g.y) < 1e30f && fabsf(g.z) < 1e30f && fabsf(g.w) < 1e30f)) return true;  // no bound
+  float pb_lo, pb_hi, pc_lo, pc_hi, qb_lo, qb_hi, qc_lo, qc_hi;
+  imul(g.x, g.y, __fsub_rd(lo[B], pr.o_up[B]), __fsub_ru(hi[B], pr.o_dn[B]), pb_lo, pb_hi);
+  imul(g.z, g.w, __fsub_rd(lo[C], pr.o_up[C]), __fsub_ru(hi[C], pr.o_dn[C]), pc_lo, pc_hi);
+  const float gap_lo = __fsub_rd(__fsub_rd(lo[A], pr.o_up[A]), __fadd_ru(pb_hi, pc_hi));
+  const float gap_hi = __fsub_ru(__fsub_ru(hi[A], pr.o_dn[A]), __fadd_rd(pb_lo, pc_lo));
+  imul(g.x, g.y, pr.d_dn[B], pr.d_up[B], qb_lo, qb_hi);
+  imul(g.z, g.w, pr.d_dn[C], pr.d_up[C], qc_lo, qc_hi);
+  const float sl_lo = __fsub_rd(pr.d_dn[A], __fadd_ru(qb_hi, qc_hi));
+  const float sl_hi = __fsub_ru(pr.d_up[A], __fadd_rd(qb_lo, qc_lo));
+  // |t| = G / D with G = -+gap > 0 and D = +-slope > 0
+  float G_lo, G_hi, D_lo, D_hi;
+  if (sl_lo > 0.0f) {
+    G_lo = -gap_hi, G_hi = -gap_lo, D_lo = sl_lo, D_hi = sl_hi;
+  } else if (sl_hi < 0.0f) {
+    G_lo = gap_lo, G_hi = gap_hi, D_lo = -sl_hi, D_hi = -sl_lo;
+  } else {
+    return true;  // the slope interval holds 0 (or is NaN): |t| is unbounded
+  }
+  if (G_hi <= 0.0f) return false;  // t >= 0 for every triangle below: ordinary hits only, the 3-D tree finds them
+  // (a NaN anywhere — inf - inf after an overflow — makes every comparison here false: the child is kept)
+  const float w_lo = fmaxf(tnear, 0.0f), w_hi = fminf(tfar, best_up);
+  // |t| <= G_hi / D_lo < w_lo,  or  |t| >= max(G_lo, 0) / D_hi > w_hi
+  if (__fmul_ru(G_hi, 1.00001f) < __fmul_rd(w_lo, D_lo)) return false;
+  if (__fmul_rd(fmaxf(G_lo, 0.0f), 0.99999f) > __fmul_ru(w_hi, D_hi)) return false;
+  return true;
+}
+
 template <int A>
 RTX_D bool box_test_prism(const float* lo, const float* hi, const RayF32& r, const PrismRay& pr, float best_up,
-                          float& tnear) {
+                          float& tnear, float4 g) {
   constexpr int B = (A + 1) % 3, C = (A + 2) % 3;
-  float tnb, tfb, tnc, tfc;
+  float tnb, tfb, tnc, tfc, tfar;
   slab<B>(lo, hi, r, tnb, tfb);
   slab<C>(lo, hi, r, tnc, tfc);
-  if (!slab_verdict(fmaxf(tnb, tnc), fminf(tfb, tfc), best_up, tnear)) return false;
-  if (!(pr.den > 0.0f)) return true;
-  const float db = fmaxf(__fsub_ru(hi[B], pr.o_dn[B]), __fsub_ru(pr.o_up[B], lo[B]));  // >= max |v_b - p_b|
-  const float dc = fmaxf(__fsub_ru(hi[C], pr.o_dn[C]), __fsub_ru(pr.o_up[C], lo[C]));
-  const float dperp = __fmul_ru(__fsqrt_ru(__fadd_ru(__fmul_ru(db, db), __fmul_ru(dc, dc))), 1.000001f);
-  const float sd = __fmul_ru(pr.s, dperp);
-  // (A): wholly ahead along a (in the direction the ray travels), and far enough that the a-term decides the
-  // sign of n.(v0 - pos)
-  const float gap = r.neg[A] ? __fsub_rd(pr.o_dn[A], hi[A]) : __fsub_rd(lo[A], pr.o_up[A]);
-  if (gap > 0.0f && __fmul_rd(gap, pr.z) > sd) return false;
-  // (B): upper bound of |t|
-  const float da = fmaxf(__fsub_ru(hi[A], pr.o_dn[A]), __fsub_ru(pr.o_up[A], lo[A]));
-  const float u = __fmul_ru(__fdiv_ru(__fadd_ru(sd, da), pr.den), 1.00001f);
-  return !(tnear > u);
+  if (!slab_verdict(fmaxf(tnb, tnc), fminf(tfb, tfc), best_up, tnear, tfar)) return false;
+  return prism_gradient_test<A>(lo, hi, pr, g, tnear, tfar, best_up);
 }
 
 // HAS_TRI = false: the caller knows the scene has no triangles, so every leaf is a sphere
@@ -217,7 +247,8 @@ RTX_D bool bvh_pop(const uint32_t* stack_ref, const float* stack_t, int& sp, dou
 // AXIS < 0: the 3-D tree; AXIS = 0..2: the prism tree that drops that axis.
 template <int AXIS, bool HAS_TRI = true>
 RTX_D void bvh_walk(const WideNode* __restrict__ nodes, const SceneView& sc, V3 pos, V3 dir, const RayInv& ri,
-                    const RayF32& rf, const PrismRay& pr, Hit& h, uint32_t* panics, TraversalCounters& tc) {
+                    const RayF32& rf, const PrismRay& pr, Hit& h, uint32_t* panics, TraversalCounters& tc,
+                    const float4* __restrict__ aux = nullptr) {
   constexpr bool PRISM = AXIS >= 0;
   constexpr int PA = PRISM ? AXIS : 0;
   uint32_t stack_ref[128];
@@ -243,8 +274,10 @@ RTX_D void bvh_walk(const WideNode* __restrict__ nodes, const SceneView& sc, V3 
       const float lo1[3] = {q1.z, q1.w, q2.x}, hi1[3] = {q2.y, q2.z, q2.w};
       const float best_up = __double2float_ru(h.t);
       float t0, t1;
-      const bool v0 = PRISM ? box_test_prism<PA>(lo0, hi0, rf, pr, best_up, t0) : box_test(lo0, hi0, rf, best_up, t0);
-      const bool v1 = PRISM ? box_test_prism<PA>(lo1, hi1, rf, pr, best_up, t1) : box_test(lo1, hi1, rf, best_up, t1);
+      float4 g0 = make_float4(0.f, 0.f, 0.f, 0.f), g1 = g0;
+      if (PRISM) g0 = __ldg(aux + 2u * cur), g1 = __ldg(aux + 2u * cur + 1u);
+      const bool v0 = PRISM ? box_test_prism<PA>(lo0, hi0, rf, pr, best_up, t0, g0) : box_test(lo0, hi0, rf, best_up, t0);
+      const bool v1 = PRISM ? box_test_prism<PA>(lo1, hi1, rf, pr, best_up, t1, g1) : box_test(lo1, hi1, rf, best_up, t1);
       if (v0 && v1) {
         const bool first0 = t0 <= t1;
         // depth <= 64 key bits + 32 index bits (Karras: every level lengthens the common prefix), so 128 holds
@@ -285,21 +318,17 @@ RTX_D Hit closest_lbvh(const SceneView& sc, const BvhView& bv, V3 pos, V3 dir, u
   tc.prims += sc.n_pl;
   // slab parameters are in units of dn, like every distance the shapes return
   const RayF32 rf = make_ray_f32(pos, ri.dn);
-  PrismRay pr;
-  pr.den = 0.0f, pr.s = 1.0f, pr.z = 0.0f;
+  PrismRay pr = make_prism_ray(pos, ri.dn);
   if (bv.root[0] != BVH_END) bvh_walk<-1, HAS_TRI>(bv.nodes[0], sc, pos, dir, ri, rf, pr, h, panics, tc);
   if (!HAS_TRI) return h;
   if (bv.root[1] != BVH_END) {
-    pr = make_prism_ray<0>(bv, pos, ri.dn);
-    bvh_walk<0>(bv.nodes[1], sc, pos, dir, ri, rf, pr, h, panics, tc);
+    bvh_walk<0>(bv.nodes[1], sc, pos, dir, ri, rf, pr, h, panics, tc, bv.aux[1]);
   }
   if (bv.root[2] != BVH_END) {
-    pr = make_prism_ray<1>(bv, pos, ri.dn);
-    bvh_walk<1>(bv.nodes[2], sc, pos, dir, ri, rf, pr, h, panics, tc);
+    bvh_walk<1>(bv.nodes[2], sc, pos, dir, ri, rf, pr, h, panics, tc, bv.aux[2]);
   }
   if (bv.root[3] != BVH_END) {
-    pr = make_prism_ray<2>(bv, pos, ri.dn);
-    bvh_walk<2>(bv.nodes[3], sc, pos, dir, ri, rf, pr, h, panics, tc);
+    bvh_walk<2>(bv.nodes[3], sc, pos, dir, ri, rf, pr, h, panics, tc, bv.aux[3]);
   }
   return h;
 }
