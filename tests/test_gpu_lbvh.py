@@ -117,6 +117,66 @@ def test_triangles_lbvh_equals_scan_including_phantoms(rtx, oracle, gpu):
     assert (ids != rtx.MISS_ID).any()  # phantom hits exist and the prism trees find them
 
 
+def test_prism_gradient_bound_stress(rtx, gpu):
+    """The prism trees prune with per-child bounds of the triangles' plane gradients (rtx_lbvh.cuh,
+    prism_gradient_test).  Configurations that stress it: planes almost parallel to the dropped axis (huge gradients),
+    exactly parallel ones (no bound), slivers, a rough height field with steep cliffs, coordinates far from the origin,
+    and phantom-heavy ray sets (origins below / behind / on the surface, grazing directions).  Ids and distance bits
+    must equal the scan's."""
+    rng = np.random.default_rng(77)
+    # (1) a rough height field with cliffs: slopes from 0 to ~40
+    g = 48
+    xs = np.linspace(-12.0, 12.0, g)
+    X, Y = np.meshgrid(xs, xs, indexing="xy")
+    Z = 5.0 + 2.0 * np.sin(0.9 * X) * np.cos(0.7 * Y) + rng.uniform(-0.4, 0.4, (g, g)) + 6.0 * (X > 3.0)
+    P = np.stack([X, Y, Z], axis=-1)
+    p00, p10, p01, p11 = P[:-1, :-1], P[:-1, 1:], P[1:, :-1], P[1:, 1:]
+    field = np.concatenate([np.stack([p00, p10, p11], axis=2).reshape(-1, 9), np.stack([p00, p11, p01], axis=2).reshape(-1, 9)])
+    # (2) a soup with near-vertical and exactly axis-parallel planes and slivers, some far away
+    soup = _visible_triangles(rng, 600, spread=15.0, size=3.0)
+    walls = []
+    for k in range(120):
+        c = rng.uniform(-10, 10, 3)
+        ax = k % 3
+        e1, e2 = np.zeros(3), np.zeros(3)
+        e1[(ax + 1) % 3] = rng.uniform(0.5, 3)
+        e2[(ax + 2) % 3] = rng.uniform(0.5, 3)
+        e2[ax] = 0.0 if k % 2 else rng.uniform(-1e-9, 1e-9)  # exactly / almost parallel to an axis
+        walls.append(np.concatenate([c, c + e1, c + e2]))
+    slivers = [np.concatenate([c, c + [3, 0, 1e-7], c + [6, 1e-7, 0]]) for c in rng.uniform(-8, 8, (40, 3))]
+    far = _visible_triangles(rng, 100, spread=5.0, size=1.0) + np.tile([4000.0, -2500.0, 900.0], 3)
+    tris = np.concatenate([field, soup, np.array(walls), np.array(slivers), far])
+    sc = rtx.Scene(rtx.Config(), rtx.Camera((0, 0, 0), (1, 0, 0), 1.0))
+    sc.add_triangles(tris, _mats(len(tris)))
+    n = 160000
+    rays = _rays(rng, n, 16.0)
+    q = n // 8
+    # origins ON triangles, directions grazing (small component along the triangle's normal)
+    t = tris[rng.integers(0, len(field), q)].reshape(q, 3, 3)
+    a = rng.uniform(0, 1, (q, 1))
+    b = rng.uniform(0, 1, (q, 1)) * (1 - a)
+    rays[:q, :3] = t[:, 0] + a * (t[:, 1] - t[:, 0]) + b * (t[:, 2] - t[:, 0])
+    graze = rng.normal(size=(q, 3))
+    graze[:, 2] = rng.uniform(0.0, 0.3, q)
+    rays[:q, 3:] = graze / np.linalg.norm(graze, axis=1, keepdims=True)
+    # origins below the field looking up, above looking up, beside looking away: everything behind or ahead
+    rays[q:2 * q, 2] = -3.0
+    rays[q:2 * q, 5] = np.abs(rays[q:2 * q, 5])
+    rays[2 * q:3 * q, 2] = 30.0
+    rays[2 * q:3 * q, 5] = np.abs(rays[2 * q:3 * q, 5])
+    rays[3 * q:4 * q, 0] = -40.0
+    rays[3 * q:4 * q, 3] = -np.abs(rays[3 * q:4 * q, 3])
+    # near the far cluster
+    rays[4 * q:5 * q, :3] = rng.uniform(-8, 8, (q, 3)) + [4000.0, -2500.0, 900.0]
+    d = rays[:, 3:]
+    rays[:, 3:] = d / np.linalg.norm(d, axis=1, keepdims=True)
+    ids = _same(sc, rtx, rays)
+    assert (ids != rtx.MISS_ID).mean() > 0.2
+    # phantom hits are among them: a hit whose plane lies behind the origin
+    tb, ib = sc.debug_closest_object(rays[q:3 * q], flags=rtx.RTX_ACCEL_BRUTE)
+    assert (ib != rtx.MISS_ID).any()
+
+
 def test_mixed_scene_with_planes_and_invalid_prims(rtx, gpu):
     rng = np.random.default_rng(23)
     sc = rtx.Scene(rtx.Config(), rtx.Camera((0, 0, 0), (1, 0, 0), 1.0))
