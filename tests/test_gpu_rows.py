@@ -99,3 +99,36 @@ def test_host_frame_and_multi_handle_on_one_gpu(rtx, gpu):
         assert got.tobytes() == ref.tobytes() and np.array_equal(ids, ref_ids)
         assert m.last_stats.rays == sc.last_stats.rays and m.last_stats.pixels == w * h
     m.close()
+
+
+def test_error_paths_of_the_multi_gpu_entry_points(rtx, gpu):
+    """Bad arguments are refused with RTX_ERR_INVALID_ARGUMENT and a message, not with a crash or a silent no-op."""
+    import ctypes as C
+    import torch
+    from rtx_b200 import HostFrame, MultiScene, scenes
+    lib = rtx._abi.load()
+    sc = scenes.sphere_demo(rays_per_pixel=2, max_bounces=2)
+    h = sc._sync()
+    pin = torch.empty((64, 64, 3), dtype=torch.float64).pin_memory()
+    st = torch.cuda.current_stream().cuda_stream
+    sh = rtx._abi.Shard(2, 2)  # index out of range
+    assert lib.rtx_scene_render_rows_to_host(h, 64, 64, 1, 0, C.byref(sh), pin.data_ptr(), None, None, st) == rtx._abi.RTX_ERR_INVALID_ARGUMENT
+    assert lib.rtx_scene_render_rows_to_host(h, 64, 64, 1, 0, None, None, None, None, st) == rtx._abi.RTX_ERR_INVALID_ARGUMENT
+    assert lib.rtx_scene_render_rows_to_host(h, 0, 64, 1, 0, None, pin.data_ptr(), None, None, st) == rtx._abi.RTX_ERR_INVALID_ARGUMENT
+    assert b"host_rgb" in lib.rtx_last_error(h) or b"size" in lib.rtx_last_error(h)
+    # more shards than strips: the extra shards own nothing and the call is a no-op for them
+    pin.fill_(-1.0)
+    for r in range(40):
+        sc.render_rows_to_host(64, 64, 3, 0, (r, 40), pin.data_ptr(), None, None, st)
+    torch.cuda.synchronize()
+    assert pin.numpy().tobytes() == sc.render(64, 64, seed=3).tobytes()
+    with pytest.raises(rtx.RtxError):
+        MultiScene(sc, [gpu, gpu])       # a device listed twice
+    with pytest.raises(rtx.RtxError):
+        MultiScene(sc, [rtx.device_count() + 3])  # no such device
+    with pytest.raises(rtx.RtxError):
+        MultiScene(sc, [])
+    with pytest.raises(rtx.RtxError):
+        HostFrame("/rtx-test-does-not-exist", 8, 8, create=False)
+    assert lib.rtx_multi_render(None, 8, 8, 0, 0, pin.data_ptr(), None, None) == rtx._abi.RTX_ERR_INVALID_ARGUMENT
+    assert lib.rtx_multi_device_count(None) == 0 and lib.rtx_multi_scene(None, 0) is None
