@@ -954,7 +954,12 @@ rtx_status rtx_scene_render_rows_to_host(rtx_scene* s, uint32_t width, uint32_t 
   // the caller's stream is done when the last copy is (and so is the scene's device frame, for the next render)
   RTX_CUDA_TRY(s, cudaEventRecord(s->ev_band[rtx_scene::MAX_BANDS], s->copy_stream));
   RTX_CUDA_TRY(s, cudaStreamWaitEvent(stream, s->ev_band[rtx_scene::MAX_BANDS], 0));
-  if (s->ev_last && cudaEventRecord(s->ev_last, stream) == cudaSuccess) s->last_stream = stream, s->last_valid = true;
+  {  // (not under graph capture: see render_common)
+    cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
+    if (cudaStreamIsCapturing(stream, &cap) != cudaSuccess) cudaGetLastError(), cap = cudaStreamCaptureStatusNone;
+    if (cap == cudaStreamCaptureStatusNone && s->ev_last && cudaEventRecord(s->ev_last, stream) == cudaSuccess)
+      s->last_stream = stream, s->last_valid = true;
+  }
   s->last_launches = launches;
   return RTX_OK;
 }
