@@ -29,7 +29,8 @@ struct rtx_multi {
     uint32_t launches = 0;
   };
   std::vector<Worker> w;
-  std::mutex mu;                 // serialises rtx_multi_render calls and guards the fields below
+  std::mutex render_mu;          // one frame at a time: held for the whole of rtx_multi_render
+  std::mutex mu;                 // guards the fields below
   std::condition_variable cv_job, cv_done;
   uint64_t generation = 0;       // bumped per frame
   uint32_t pending = 0;          // workers still busy with the current frame
@@ -189,8 +190,8 @@ rtx_status rtx_multi_render(rtx_multi* m, uint32_t width, uint32_t height, uint6
   if (!m) return fail(nullptr, RTX_ERR_INVALID_ARGUMENT, "null multi handle");
   if (!out_rgb) return fail(nullptr, RTX_ERR_INVALID_ARGUMENT, "out_rgb is null");
   const auto t0 = std::chrono::steady_clock::now();
+  std::lock_guard<std::mutex> frame(m->render_mu);  // a concurrent caller's frame finishes first, results and all
   std::unique_lock<std::mutex> lk(m->mu);
-  m->cv_done.wait(lk, [&] { return m->pending == 0; });  // a concurrent caller's frame
   m->width = width, m->height = height, m->seed = seed, m->flags = flags, m->out_rgb = out_rgb, m->out_ids = out_ids;
   m->pending = (uint32_t)m->w.size();
   ++m->generation;

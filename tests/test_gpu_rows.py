@@ -132,3 +132,33 @@ def test_error_paths_of_the_multi_gpu_entry_points(rtx, gpu):
         HostFrame("/rtx-test-does-not-exist", 8, 8, create=False)
     assert lib.rtx_multi_render(None, 8, 8, 0, 0, pin.data_ptr(), None, None) == rtx._abi.RTX_ERR_INVALID_ARGUMENT
     assert lib.rtx_multi_device_count(None) == 0 and lib.rtx_multi_scene(None, 0) is None
+
+
+def test_multi_render_from_two_threads(rtx, gpu):
+    """rtx_multi_render is one frame at a time inside the library: two threads rendering different seeds through one
+    handle each get their own frame and their own statistics."""
+    import threading
+    from rtx_b200 import MultiScene, scenes
+    sc = scenes.sphere_demo(rays_per_pixel=3, max_bounces=5)
+    w, h = 160, 100
+    want = {seed: (sc.render(w, h, seed=seed), sc.last_stats.rays) for seed in (31, 32)}
+    m = MultiScene(sc, [gpu])
+    out = {}
+    lock = threading.Lock()
+
+    def work(seed):
+        import ctypes as C
+        for _ in range(6):
+            rgb = np.empty((h, w, 3), dtype=np.float64)
+            st = rtx._abi.Stats()
+            rc = rtx._abi.load().rtx_multi_render(m._handle, w, h, seed, 0, rgb.ctypes.data, None, C.byref(st))
+            with lock:
+                out.setdefault(seed, []).append((rc, rgb.tobytes(), st.rays))
+    th = [threading.Thread(target=work, args=(s,)) for s in (31, 32)]
+    [t.start() for t in th]
+    [t.join() for t in th]
+    for seed in (31, 32):
+        assert len(out[seed]) == 6
+        for rc, raw, rays in out[seed]:
+            assert rc == 0 and raw == want[seed][0].tobytes() and rays == want[seed][1]
+    m.close()
