@@ -462,6 +462,8 @@ rtx_status rtx_scene_render_preview_f32(rtx_scene* s, uint32_t width, uint32_t h
     RTX_CUDA_TRY(s, cudaMalloc((void**)&s->d_ids, npix * 4));
     s->d_ids_cap = npix * 4;
   }
+  // the scene's device frame is shared with the f64 entry points: wait for whatever they last enqueued elsewhere
+  if (s->last_valid && s->last_stream != s->stream && s->ev_last) RTX_CUDA_TRY(s, cudaStreamWaitEvent(s->stream, s->ev_last, 0));
   RTX_CUDA_TRY(s, cudaMemsetAsync(s->d_counters, 0, 8 * sizeof(unsigned long long), s->stream));
   RTX_CUDA_TRY(s, cudaEventRecord(s->ev0, s->stream));
   const rtx_status st = preview_launch(s, width, height, reinterpret_cast<float*>(s->d_rgb), out_first_hit_id ? s->d_ids : nullptr,
