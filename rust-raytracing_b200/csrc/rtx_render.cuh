@@ -68,7 +68,9 @@ struct Granule {
   uint32_t x0, y0, w, npix, base_out, tx0, ty0;
 };
 // gidx = index of the granule within this shard's unit list (local unit = gidx / grans_per_unit).
-__device__ __forceinline__ Granule decode_granule(const RenderParams& p, uint32_t gidx) {
+// (out of line: once per queue entry, two runtime divisions — not worth a place in loops that are larger than the
+// instruction cache)
+static __device__ __noinline__ Granule decode_granule(const RenderParams& p, uint32_t gidx) {
   Granule g;
   if (p.strip_mode) {  // (warp-uniform)
     const uint32_t lstrip = p.tile_first + gidx / p.grans_per_unit, col = gidx % p.grans_per_unit;
@@ -95,15 +97,17 @@ __device__ __forceinline__ Granule decode_granule(const RenderParams& p, uint32_
   g.base_out = ltile * (TILE * TILE);
   return g;
 }
+static __device__ __noinline__ uint32_t ragged_div(uint32_t k, uint32_t w) { return k / w; }
 // pixel k (row-major inside the granule) → image pixel index and output index
 __device__ __forceinline__ void granule_pixel(const RenderParams& p, const Granule& g, uint32_t k, uint32_t* x, uint32_t* y,
                                               uint32_t* out_index) {
   if (g.w == GRAN_W) {  // (warp-uniform) a full-width granule: no division
     *x = g.x0 + (k & (GRAN_W - 1u));
     *y = g.y0 + k / GRAN_W;
-  } else {
-    *x = g.x0 + k % g.w;
-    *y = g.y0 + k / g.w;
+  } else {  // the image's ragged right edge
+    const uint32_t q = ragged_div(k, g.w);
+    *x = g.x0 + (k - q * g.w);
+    *y = g.y0 + q;
   }
   *out_index = p.compact ? g.base_out + (*y - g.ty0) * TILE + (*x - g.tx0) : *y * p.width + *x;
 }
