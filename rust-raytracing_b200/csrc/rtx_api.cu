@@ -112,6 +112,27 @@ static void build_sphere_cull(const std::vector<double>& sph, std::vector<float>
   *r2max = finite ? std::nextafterf((float)r2, inf) : inf;
 }
 
+// The sphere cull's margins for a whole launch (SceneLayout::cull_*): the formulas of sphere_cull_setup (rtx_trace.cuh)
+// with R = pmax + sph_cmax, D1 = sqrt(3) and a = 1 + 1e-6, every step rounded up (computed in double, then to the next
+// float above).  pmax covers the camera and four times the spheres' extent: bounce rays start on objects, and the few
+// that start far out on an unbounded plane fall back to "keep every sphere".
+void cull_constants(SceneLayout* L, const rtx_camera& cam) {
+  L->cull_pmax = 0.0f, L->cull_neg_mq = 0.0f, L->cull_mh = 0.0f;
+  const double cmax = L->sph_cmax, r2max = L->sph_r2max;
+  const double camax = std::fmax(std::fabs(cam.position.x), std::fmax(std::fabs(cam.position.y), std::fabs(cam.position.z)));
+  const double pmax = std::fmax(4.0 * cmax + 16.0, 2.0 * camax + 1.0);
+  if (!(pmax < 1e15) || !(r2max < 1e30) || L->n_sph == 0) return;  // non-finite or huge: per-ray margins
+  const double up = 1.0 + 1e-6;
+  const double R = (pmax * up + cmax) * up;
+  const double rd = R * 1.7320508075688774 * up;
+  const double B = (rd * rd + (1.0 + 1e-6) * (3.0 * R * R + r2max)) * up;
+  if (!(B < 1e37)) return;
+  const float inf = std::numeric_limits<float>::infinity();
+  L->cull_pmax = std::nextafterf((float)pmax, 0.0f);  // (rounded DOWN: the test is pmax_ray <= cull_pmax)
+  L->cull_neg_mq = -std::nextafterf((float)(B * 1.9073486328125e-6 * up + 1e-30), inf);
+  L->cull_mh = std::nextafterf((float)(rd * 9.5367431640625e-7 * up + 1e-30), inf);
+}
+
 rtx_status ensure_uploaded(rtx_scene* s, cudaStream_t stream) {
   if (!s->dirty && s->d_blob) {
     const bool any = !s->upd_sph.empty() || !s->upd_pl.empty() || !s->upd_tri.empty() || !s->upd_mat.empty();
@@ -352,6 +373,7 @@ static rtx_status render_common_on_stream(rtx_scene* s, uint32_t width, uint32_t
   p.cos_y = p.sin_y + height;
   p.scene_blob = s->d_blob;
   p.layout = s->layout;
+  cull_constants(&p.layout, s->camera);
   p.use_bvh = use_bvh ? 1u : 0u;
   p.lane_kernel = (flags & RTX_FLAG_LANE_KERNEL) ? 1u : 0u;
   p.queue_mode = (flags & RTX_FLAG_PIXEL_QUEUE) ? 1u : ((flags & RTX_FLAG_SAMPLE_QUEUE) ? 2u : 0u);

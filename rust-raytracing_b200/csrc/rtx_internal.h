@@ -100,6 +100,8 @@ rtx_status cuda_fail(const rtx_scene* s, cudaError_t e, const char* what);
 // Uploads the packed scene if it changed; fills s->layout.  Asynchronous on `stream`.
 rtx_status ensure_uploaded(rtx_scene* s, cudaStream_t stream);
 // Builds (or reuses) the sin/cos tables for this image size.  Asynchronous on `stream`.
+// Per-launch margins of the scan's sphere cull (SceneLayout::cull_*)
+void cull_constants(SceneLayout* L, const rtx_camera& cam);
 rtx_status ensure_tables(rtx_scene* s, uint32_t width, uint32_t height, cudaStream_t stream);
 cudaError_t launch_render(const RenderParams& p, int sm_count, cudaStream_t stream, uint32_t* out_launches);
 // RTX_FLAG_RNG_ROW: one thread per image row, one RNG stream per row (rtx_render.cu)

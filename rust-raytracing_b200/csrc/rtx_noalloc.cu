@@ -96,6 +96,7 @@ extern "C" rtx_status rtx_scene_render_device_noalloc(rtx_scene* s, uint32_t wid
   p.cos_y = p.sin_y + height;
   p.scene_blob = s->d_blob;
   p.layout = s->layout;
+  cull_constants(&p.layout, s->camera);
   p.queue_mode = 2;  // the sample queue: the kernel pair that uses scratch
   p.shard_index = 0, p.shard_count = 1;
   p.tiles_x = (width + TILE - 1) / TILE, p.tiles_y = (height + TILE - 1) / TILE;

@@ -46,6 +46,12 @@ struct SceneLayout {
   // Scene-wide bounds for the f32 cull (rtx_trace.cuh, SphereCull): max |centre component| and max r*r over
   // all spheres, rounded up; +inf when a sphere is not finite (then nothing is ever culled).
   float sph_cmax, sph_r2max;
+  // Per launch (cull_constants, rtx_api.cu): the cull's two margins for every ray whose origin has no component larger
+  // than cull_pmax — computed once on the host from the bounds R = cull_pmax + sph_cmax, D1 <= sqrt(3), a <= 1 + 1e-6
+  // instead of per ray from the ray's own |p|, D1 and a.  Larger R, D1, a only widen the margins (SphereCull's error
+  // bounds are monotone in them), so the cull stays a proof; an origin beyond cull_pmax (a far hit on an unbounded
+  // plane) switches the cull off for that ray.  cull_pmax = 0: per-ray margins (debug kernels).
+  float cull_pmax, cull_neg_mq, cull_mh;
 };
 
 struct SceneView {
@@ -58,6 +64,7 @@ struct SceneView {
   const uint32_t* tri_id;
   const float* sph32;
   float sph_cmax, sph_r2max;
+  float cull_pmax, cull_neg_mq, cull_mh;
   uint32_t n_obj, n_sph, n_pl, n_tri;
 };
 
@@ -73,6 +80,7 @@ RTX_HD SceneView make_view(const unsigned char* base, const SceneLayout& L) {
   v.sph32 = reinterpret_cast<const float*>(base + L.off_sph32);
   v.sph_cmax = L.sph_cmax;
   v.sph_r2max = L.sph_r2max;
+  v.cull_pmax = L.cull_pmax, v.cull_neg_mq = L.cull_neg_mq, v.cull_mh = L.cull_mh;
   v.n_obj = L.n_obj;
   v.n_sph = L.n_sph;
   v.n_pl = L.n_pl;

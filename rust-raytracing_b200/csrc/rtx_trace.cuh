@@ -225,6 +225,12 @@ RTX_D SphereCull sphere_cull_setup(const SceneView& sc, V3 pos, const RayInv& ri
   k.dx = __double2float_rn(ri.dn.x), k.dy = __double2float_rn(ri.dn.y), k.dz = __double2float_rn(ri.dn.z);
   k.a = __double2float_ru(ri.a);
   const float pmax = fmaxf(fmaxf(fabsf(k.px), fabsf(k.py)), fabsf(k.pz));
+  if (sc.cull_pmax > 0.0f) {  // (warp-uniform) margins precomputed per launch for origins within cull_pmax
+    const bool in = pmax <= sc.cull_pmax && k.a <= 1.000001f;
+    k.neg_mq = in ? sc.cull_neg_mq : CUDART_NAN_F;
+    k.mh = in ? sc.cull_mh : CUDART_NAN_F;
+    return k;
+  }
   const float R = __fadd_ru(pmax, sc.sph_cmax);
   const float rd = __fmul_ru(R, __fadd_ru(__fadd_ru(fabsf(k.dx), fabsf(k.dy)), fabsf(k.dz)));
   const float B = __fmaf_ru(rd, rd, __fmul_ru(fabsf(k.a), __fmaf_ru(__fmul_ru(3.0f, R), R, sc.sph_r2max)));
