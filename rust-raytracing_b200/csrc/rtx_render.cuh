@@ -68,9 +68,7 @@ struct Granule {
   uint32_t x0, y0, w, npix, base_out, tx0, ty0;
 };
 // gidx = index of the granule within this shard's unit list (local unit = gidx / grans_per_unit).
-// (out of line: once per queue entry, two runtime divisions — not worth a place in loops that are larger than the
-// instruction cache)
-static __device__ __noinline__ Granule decode_granule(const RenderParams& p, uint32_t gidx) {
+__device__ __forceinline__ Granule decode_granule(const RenderParams& p, uint32_t gidx) {
   Granule g;
   if (p.strip_mode) {  // (warp-uniform)
     const uint32_t lstrip = p.tile_first + gidx / p.grans_per_unit, col = gidx % p.grans_per_unit;
@@ -97,6 +95,10 @@ static __device__ __noinline__ Granule decode_granule(const RenderParams& p, uin
   g.base_out = ltile * (TILE * TILE);
   return g;
 }
+// The same out of line, for the context-pool kernel: once per queue entry, two runtime divisions — not worth a place
+// in a loop that is larger than the instruction cache (the lane kernel and the per-thread kernels keep it inline:
+// primary-only frames decode a granule per ~150 warp instructions, and a call there costs 4 %).
+static __device__ __noinline__ Granule decode_granule_cold(const RenderParams& p, uint32_t gidx) { return decode_granule(p, gidx); }
 static __device__ __noinline__ uint32_t ragged_div(uint32_t k, uint32_t w) { return k / w; }
 // pixel k (row-major inside the granule) → image pixel index and output index
 __device__ __forceinline__ void granule_pixel(const RenderParams& p, const Granule& g, uint32_t k, uint32_t* x, uint32_t* y,

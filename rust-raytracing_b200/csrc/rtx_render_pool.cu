@@ -305,7 +305,7 @@ __global__ void __launch_bounds__(POOL_WARPS * 32, MIN_BLOCKS) __maxnreg__(pool_
             gidx = tg;
             g_slot_base = (tg * rpp + g_sample) * GRAN_PIXELS;
           }
-          g = decode_granule(p, gidx);
+          g = decode_granule_cold(p, gidx);
           g_next = 0;
           continue;  // re-check (the granule may be empty at the image border)
         }
