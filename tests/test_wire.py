@@ -115,3 +115,25 @@ def test_wire_scene_renders_like_the_f32_rounded_scene(rtx, oracle, gpu):
         assert out.tobytes() == ia.tobytes()
     finally:
         lib.rtx_scene_destroy(h)
+
+
+@pytest.mark.gpu
+def test_wire_scene_previews_as_the_wgpu_backend_would(rtx, oracle, gpu):
+    """The reference's own use of these bytes: gpu::Scene uploads them and base_shader.wgsl renders them.  A scene
+    ingested from the f32 wire format and rendered with rtx_scene_render_preview_f32 equals the WGSL oracle's render of
+    those f32 values — narrowing the widened doubles back to f32 is exact, so nothing is rounded twice."""
+    from rtx_b200 import wire
+    sc, (types, shapes, mats) = _demo(rtx)
+    cam, cfg = sc.camera, sc.config
+    pos = (cam._c.position.x, cam._c.position.y, cam._c.position.z)
+    dr = (cam._c.direction.x, cam._c.direction.y, cam._c.direction.z)
+    records, buffers = wire.serialize_scene(types, shapes, mats)
+    a = rtx.Scene.from_wire(wire.serialize_camera(pos, dr, cam._c.fov),
+                            wire.serialize_config(cfg.rays_per_pixel, cfg.max_bounces, cfg.focal_length, cfg.focal_offset,
+                                                  cfg.non_focal_offset), records, buffers)
+    rgb, ids = a.render_preview(160, 96, want_ids=True)
+    ref = oracle.render_preview_scene(a, 160, 96)
+    assert np.array_equal(ids, ref["ids"]) and rgb.tobytes() == ref["rgb"].tobytes() and a.last_stats.rays == ref["rays"]
+    # the struct-built scene holds the unrounded doubles: its preview narrows them itself — to the same f32 values
+    rgb2 = sc.render_preview(160, 96)
+    assert rgb2.tobytes() == rgb.tobytes()
