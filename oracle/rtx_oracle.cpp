@@ -4,10 +4,11 @@
 // import, link or execute this file.  Allowed users: tests/, __graft_entry__.smoke(), and bench.py's
 // cpu_baseline / --impl reference legs.
 //
-// PARITY STATUS: "parity unpinned" at the RNG boundary and for every intersection/shading routine —
-// the reference ships no golden vectors for them.  The only reference-owned known
-// answers on this path are the 12 exact assertions of the 4 camera tests (src/raytracing/camera.rs:79-110),
-// which tests/test_oracle.py replays against this file.  The reference (Rust) cannot be compiled in this
+// PARITY STATUS: "parity unpinned" for every intersection/shading routine and for the f64 mantissa fill of the
+// RNG — the reference ships no golden vectors for them.  Pinned: the 12 exact assertions of the
+// 4 camera tests (src/raytracing/camera.rs:79-110), which tests/test_oracle.py replays against this file, and — since
+// round 2 — the RNG's u64 stream, against the machine code of fastrand 2.3.0 (the reference's Cargo.lock pin) as
+// compiled into wheels of this image (tests/test_fastrand_pin.py).  The reference (Rust) cannot be compiled in this
 // image (no cargo/rustc), so fidelity is argued line by line: every function cites the reference lines it
 // restates, and keeps the reference's exact IEEE-754 f64 evaluation order.
 //
@@ -100,6 +101,9 @@ inline V3 matvec(const M3& m, V3 v) { return {dot(v, m.x), dot(v, m.y), dot(v, m
 
 // ---------------------------------------------------------------------------------------------
 // fastrand 2.3.0 (third-party; restated) — call sites math/vector.rs:31-33,37-38
+// gen_u64 is pinned: tests/test_fastrand_pin.py executes the machine code of this step as compiled into hf_xet 1.5.0
+// (whose SBOM lists pkg:cargo/fastrand@2.3.0, the reference's Cargo.lock pin) and gets this stream bit for bit.
+// f64()'s mantissa fill is restated from the published source; nothing in this image holds a compiled copy of it.
 // ---------------------------------------------------------------------------------------------
 struct WyRand {
   uint64_t s;
