@@ -34,10 +34,93 @@ constexpr int RENDER_BLOCK = 256;
 constexpr int BVH_BLOCKS_PER_SM = RTX_BVH_BLOCKS_PER_SM;
 constexpr uint32_t FULL = 0xFFFFFFFFu;
 
-template <bool SMEM_SCENE, bool USE_BVH, bool HAS_TRI = true>
+// K2 for scanned scenes whose blob does not fit the shared-memory stage (> 64 KB): the sphere arrays — the bulk of such
+// a scene — go through shared memory CHUNK by chunk.  One CTA = one chunk pipeline: thread 0 issues three TMA bulk copies
+// per chunk (f32 cull records, f64 records, object ids) into one of two buffers while every thread scans the other for
+// its own ray; an mbarrier per buffer, a __syncthreads() per chunk.  That makes the nearest-hit query a CTA-wide step
+// (every thread takes part in the barriers, with or without a ray), so the CHUNKED instantiation of the kernel leaves
+// its loop on a CTA-wide vote.  Planes, triangles and materials stay where they are (L1/L2).
+constexpr uint32_t CHUNK_SPHERES = 1024;
+constexpr uint32_t CHUNK_BYTES = CHUNK_SPHERES * (SPH_STRIDE * 8 + SPH_STRIDE * 4 + 4);  // 52 KB per buffer
+struct ChunkPipe {
+  unsigned char* buf;  // [2][CHUNK_BYTES]: f64 records | f32 records | ids
+  uint64_t* mbar;      // [2]
+  uint32_t uses;       // chunks loaded so far (the same number in every thread)
+};
+__device__ __forceinline__ void chunk_issue(const ChunkPipe& cp, const SceneView& sc, uint32_t c, uint32_t use) {
+  if (threadIdx.x != 0) return;
+  const uint32_t b = use & 1u, first = c * CHUNK_SPHERES, n = min(CHUNK_SPHERES, sc.n_sph - first);
+  unsigned char* dst = cp.buf + (size_t)b * CHUNK_BYTES;
+  const uint32_t bytes64 = n * SPH_STRIDE * 8u, bytes32 = n * SPH_STRIDE * 4u, bytes_id = (n * 4u + 15u) & ~15u;
+  const uint32_t bar = smem_u32(cp.mbar + b);
+  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // the buffer was read through the generic proxy
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes64 + bytes32 + bytes_id) : "memory");
+  auto copy = [&](unsigned char* d, const void* s, uint32_t bytes) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_u32(d)),
+                 "l"(s), "r"(bytes), "r"(bar)
+                 : "memory");
+  };
+  copy(dst, sc.sph + (size_t)first * SPH_STRIDE, bytes64);
+  copy(dst + CHUNK_SPHERES * SPH_STRIDE * 8u, sc.sph32 + (size_t)first * SPH_STRIDE, bytes32);
+  copy(dst + CHUNK_SPHERES * SPH_STRIDE * 12u, sc.sph_id + first, bytes_id);
+}
+__device__ __forceinline__ void chunk_wait(const ChunkPipe& cp, uint32_t use) {
+  const uint32_t bar = smem_u32(cp.mbar + (use & 1u)), parity = (use >> 1) & 1u;
+  asm volatile(
+      "{\n"
+      ".reg .pred P1;\n"
+      "CHUNK_WAIT:\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 P1, [%0], %1;\n"
+      "@P1 bra CHUNK_DONE;\n"
+      "bra CHUNK_WAIT;\n"
+      "CHUNK_DONE:\n"
+      "}\n" ::"r"(bar),
+      "r"(parity)
+      : "memory");
+}
+// scene.rs:243-251 for every thread of the CTA at once (active = this thread has a ray).  Same Hit as closest_brute.
+template <bool HAS_TRI>
+__device__ __forceinline__ Hit closest_chunked(ChunkPipe& cp, const SceneView& sc, bool active, V3 pos, V3 dir, uint32_t* panics) {
+  Hit h;
+  h.t = CUDART_INF;
+  h.id = MISS_ID;
+  h.ref = 0;
+  const RayInv ri = ray_invariants(dir);
+  const SphereCull cull = sphere_cull_setup(sc, pos, ri);
+  const uint32_t n_chunks = (sc.n_sph + CHUNK_SPHERES - 1u) / CHUNK_SPHERES;
+  if (n_chunks) chunk_issue(cp, sc, 0u, cp.uses);
+  for (uint32_t c = 0; c < n_chunks; ++c) {
+    if (c + 1u < n_chunks) chunk_issue(cp, sc, c + 1u, cp.uses + 1u);  // its buffer was released by the barrier of chunk c - 1
+    chunk_wait(cp, cp.uses);
+    if (active) {
+      const unsigned char* b = cp.buf + (size_t)(cp.uses & 1u) * CHUNK_BYTES;
+      const uint32_t first = c * CHUNK_SPHERES;
+      scan_spheres(reinterpret_cast<const float*>(b + CHUNK_SPHERES * SPH_STRIDE * 8u), reinterpret_cast<const double*>(b),
+                   reinterpret_cast<const uint32_t*>(b + CHUNK_SPHERES * SPH_STRIDE * 12u), first,
+                   min(CHUNK_SPHERES, sc.n_sph - first), pos, ri, cull, h);
+    }
+    __syncthreads();
+    ++cp.uses;
+  }
+  if (active) scan_planes_triangles<HAS_TRI>(sc, pos, dir, ri, h, panics);
+  return h;
+}
+
+template <bool SMEM_SCENE, bool USE_BVH, bool HAS_TRI = true, bool CHUNKED = false>
 __global__ void __launch_bounds__(RENDER_BLOCK, USE_BVH ? BVH_BLOCKS_PER_SM : 2) render_megakernel(const __grid_constant__ RenderParams p) {
+  static_assert(!CHUNKED || (!SMEM_SCENE && !USE_BVH), "chunked staging is for scanned scenes too large to stage whole");
   extern __shared__ __align__(128) unsigned char smem_raw[];
   const unsigned char* base = p.scene_blob;
+  ChunkPipe cp;
+  cp.buf = smem_raw + 128, cp.mbar = reinterpret_cast<uint64_t*>(smem_raw), cp.uses = 0;
+  if (CHUNKED) {
+    if (threadIdx.x == 0) {
+      asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(smem_u32(cp.mbar)));
+      asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(smem_u32(cp.mbar + 1)));
+      asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
+  }
   if (SMEM_SCENE) {
     uint64_t* mbar = reinterpret_cast<uint64_t*>(smem_raw);
     unsigned char* dst = smem_raw + 128;
@@ -122,7 +205,11 @@ __global__ void __launch_bounds__(RENDER_BLOCK, USE_BVH ? BVH_BLOCKS_PER_SM : 2)
       g_next = min(g_next + (uint32_t)__popc(need), g_npix);
       need = __ballot_sync(FULL, !have_pixel);
     }
-    if (!__any_sync(FULL, have_pixel)) break;  // queue exhausted and every lane is done
+    if (CHUNKED) {
+      if (!__syncthreads_or(have_pixel ? 1 : 0)) break;  // the nearest-hit query below is a CTA-wide step
+    } else if (!__any_sync(FULL, have_pixel)) {
+      break;  // queue exhausted and every lane is done
+    }
 
     // ---- 2. start the next camera sample (scene.rs:199-210) ----
     if (have_pixel && !alive) {
@@ -140,12 +227,17 @@ __global__ void __launch_bounds__(RENDER_BLOCK, USE_BVH ? BVH_BLOCKS_PER_SM : 2)
     }
 
     // ---- 3. one segment of render_ray (scene.rs:227-240) ----
+    Hit hc;
+    hc.t = CUDART_INF, hc.id = MISS_ID, hc.ref = 0;
+    if (CHUNKED) hc = closest_chunked<HAS_TRI>(cp, sc, alive && sc.n_obj != 0, pos, dir, &n_panics);
     if (alive) {
       bool end = false;
       if (sc.n_obj == 0) {
         end = true;  // scene.rs:224-226
       } else {
-        const Hit h = USE_BVH ? closest_lbvh<HAS_TRI>(sc, p.bvh, pos, dir, &n_panics, tc) : closest_brute<HAS_TRI>(sc, pos, dir, &n_panics);
+        const Hit h = CHUNKED ? hc
+                              : (USE_BVH ? closest_lbvh<HAS_TRI>(sc, p.bvh, pos, dir, &n_panics, tc)
+                                         : closest_brute<HAS_TRI>(sc, pos, dir, &n_panics));
         ++n_rays;
         if (segment == 0 && sample == 0 && p.out_ids) p.out_ids[out_index] = h.id;
         if (h.id == MISS_ID) {
@@ -303,7 +395,9 @@ cudaError_t launch_render(const RenderParams& p, int sm_count, cudaStream_t stre
   if (!p.lane_kernel && pool_kernel_eligible(p)) return launch_render_pool(p, sm_count, stream, out_launches);
   constexpr uint32_t SMEM_LIMIT = 64u * 1024u;
   const bool use_smem = p.layout.bytes > 0 && p.layout.bytes <= SMEM_LIMIT;
-  const size_t smem = use_smem ? (size_t)p.layout.bytes + 128 : 0;
+  // a scanned scene beyond the stage with enough spheres to matter: chunked staging (two 52 KB buffers per CTA)
+  const bool chunked = !use_smem && !p.use_bvh && p.layout.n_sph >= 256;
+  const size_t smem = use_smem ? (size_t)p.layout.bytes + 128 : (chunked ? 128 + 2 * (size_t)CHUNK_BYTES : 0);
   cudaError_t e = cudaSuccess;
   const int blocks_per_sm = p.use_bvh ? BVH_BLOCKS_PER_SM : 2;
   const uint64_t total_work = (uint64_t)p.my_tiles * p.grans_per_unit;
@@ -321,7 +415,9 @@ cudaError_t launch_render(const RenderParams& p, int sm_count, cudaStream_t stre
   };
   // specialised on triangle-free scenes (C3): the triangle code and its registers are compiled out
   const bool tri = p.layout.n_tri != 0;
-  if (use_smem)
+  if (chunked)
+    e = tri ? launch(render_megakernel<false, false, true, true>) : launch(render_megakernel<false, false, false, true>);
+  else if (use_smem)
     e = p.use_bvh ? (tri ? launch(render_megakernel<true, true, true>) : launch(render_megakernel<true, true, false>))
                   : (tri ? launch(render_megakernel<true, false, true>) : launch(render_megakernel<true, false, false>));
   else

@@ -251,24 +251,17 @@ RTX_D bool sphere_cull_keep(const float* __restrict__ rec32, const SphereCull& k
   return !(q <= k.neg_mq) && !(h >= k.mh);
 }
 
-// scene.rs:243-251 — brute-force scan over all three shape arrays.
-// HAS_TRI = false: the caller knows the scene has no triangles (the loop and its registers are compiled out)
-template <bool HAS_TRI = true>
-RTX_D Hit closest_brute(const SceneView& sc, V3 pos, V3 dir, uint32_t* panics) {
-  Hit h;
-  h.t = CUDART_INF;
-  h.id = MISS_ID;
-  h.ref = 0;
-  const RayInv ri = ray_invariants(dir);
-  // Spheres, in chunks of 32: a branch-free f32 pass (SphereCull) records as one bit each the spheres that
-  // cannot be ruled out; those few (usually 0-2 per ray) then go through the exact f64 test and, if it passes,
-  // the sqrt + division of the root.  `consider` is a lexicographic (t, id) minimum, so the visiting order
-  // is irrelevant.
-  const SphereCull cull = sphere_cull_setup(sc, pos, ri);
-  for (uint32_t base = 0; base < sc.n_sph; base += 32u) {
-    const uint32_t cnt = min(32u, sc.n_sph - base);
-    const double* __restrict__ chunk = sc.sph + (size_t)base * SPH_STRIDE;
-    const float* __restrict__ chunk32 = sc.sph32 + (size_t)base * SPH_STRIDE;
+// The sphere part of the scan over `n` spheres whose records start at sph32 / sph / ids (the scene's arrays, or a chunk
+// of them staged in shared memory); first = scene index of the first one.  In batches of 32: a branch-free f32 pass
+// (SphereCull) records as one bit each the spheres that cannot be ruled out; those few (usually 0-2 per ray) then go
+// through the exact f64 test and, if it passes, the sqrt + division of the root.  `consider` is a lexicographic
+// (t, id) minimum, so the visiting order is irrelevant.
+RTX_D void scan_spheres(const float* __restrict__ sph32, const double* __restrict__ sph, const uint32_t* __restrict__ ids,
+                        uint32_t first, uint32_t n, V3 pos, const RayInv& ri, const SphereCull& cull, Hit& h) {
+  for (uint32_t base = 0; base < n; base += 32u) {
+    const uint32_t cnt = min(32u, n - base);
+    const double* __restrict__ chunk = sph + (size_t)base * SPH_STRIDE;
+    const float* __restrict__ chunk32 = sph32 + (size_t)base * SPH_STRIDE;
     uint32_t cand = 0u;
     // (not unrolled: the pool kernel's hot loop is larger than the instruction cache, and every copy of this body costs
     // more in fetch stalls than it saves in loop overhead — C2 10.43 ms at unroll 2, 10.35 at 1, 10.66 at 3, 11.01 at 6)
@@ -279,9 +272,13 @@ RTX_D Hit closest_brute(const SceneView& sc, V3 pos, V3 dir, uint32_t* panics) {
       cand &= cand - 1u;
       double hh, qq;
       if (sphere_candidate(chunk + (size_t)j * SPH_STRIDE, pos, ri, &hh, &qq))
-        consider(h, sphere_root(hh, qq, ri), sc.sph_id[base + j], REF_SPHERE | (base + j));
+        consider(h, sphere_root(hh, qq, ri), ids[base + j], REF_SPHERE | (first + base + j));
     }
   }
+}
+// ... and the planes and triangles.
+template <bool HAS_TRI = true>
+RTX_D void scan_planes_triangles(const SceneView& sc, V3 pos, V3 dir, const RayInv& ri, Hit& h, uint32_t* panics) {
   for (uint32_t i = 0; i < sc.n_pl; ++i) {
     double t;
     if (plane_distance(sc.pl + (size_t)i * PL_STRIDE, pos, ri, &t)) consider(h, t, sc.pl_id[i], REF_PLANE | i);
@@ -293,6 +290,20 @@ RTX_D Hit closest_brute(const SceneView& sc, V3 pos, V3 dir, uint32_t* panics) {
       consider(h, t, sc.tri_id[i], REF_TRIANGLE | i);
     if (panic) ++*panics;
   }
+}
+
+// scene.rs:243-251 — brute-force scan over all three shape arrays.
+// HAS_TRI = false: the caller knows the scene has no triangles (the loop and its registers are compiled out)
+template <bool HAS_TRI = true>
+RTX_D Hit closest_brute(const SceneView& sc, V3 pos, V3 dir, uint32_t* panics) {
+  Hit h;
+  h.t = CUDART_INF;
+  h.id = MISS_ID;
+  h.ref = 0;
+  const RayInv ri = ray_invariants(dir);
+  const SphereCull cull = sphere_cull_setup(sc, pos, ri);
+  scan_spheres(sc.sph32, sc.sph, sc.sph_id, 0u, sc.n_sph, pos, ri, cull, h);
+  scan_planes_triangles<HAS_TRI>(sc, pos, dir, ri, h, panics);
   return h;
 }
 
