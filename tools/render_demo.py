@@ -2,7 +2,7 @@
 """render_demo.py — writes the sphere demo scene (S1) as binary PPM files, headless: the f64 path through
 rtx_scene_render_to_rgb8 (≙ Scene::render_to_image, scene.rs:173-178) and the f32 preview (the wgpu backend's arithmetic,
 quantised the same way — note that the reference's shader mirrors the picture left-right relative to its CPU path:
-base_shader.wgsl:70 crosses with (0,0,1), camera.rs:44 with (0,0,-1)).  Usage: python tools/render_demo.py [width height spp] -> demo_f64.ppm, demo_preview.ppm"""
+base_shader.wgsl:71 crosses with (0,0,1), camera.rs:44 with (0,0,-1)).  Usage: python tools/render_demo.py [width height spp] -> demo_f64.ppm, demo_preview.ppm"""
 import os
 import sys
 
