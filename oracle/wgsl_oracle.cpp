@@ -63,10 +63,10 @@ struct Scene {
   uint64_t n;
 };
 
-// base_shader.wgsl:97-142
+// base_shader.wgsl:99-142
 struct Rng {
   uint32_t seed;
-  static uint32_t jenkins(uint32_t x) {  // :117-125
+  static uint32_t jenkins(uint32_t x) {  // :115-123
     x += x << 10;
     x ^= x >> 6;
     x += x << 3;
@@ -74,21 +74,21 @@ struct Rng {
     x += x << 15;
     return x;
   }
-  void init(float ux, float uy) {  // :97-116
+  void init(float ux, float uy) {  // :99-114
     const float ax = std::fmin(std::fmax(ux + 0.5f, 0.0f), 0.999999f), ay = std::fmin(std::fmax(uy + 0.5f, 0.0f), 0.999999f);
     const uint32_t ai = (uint32_t)(ax * 4294967296.0f), bi = (uint32_t)(ay * 4294967296.0f);
     uint32_t h = ai ^ (bi * 0x85ebca6bu);
     h = (h ^ (h >> 16)) * 0x85ebca6bu;
     seed = jenkins(h ^ (h >> 13));
   }
-  uint32_t next_u32() {  // :126-131
+  uint32_t next_u32() {  // :124-129
     const uint32_t s = seed * 747796405u + 2891336453u;
     seed = s;
     const uint32_t word = ((s >> ((s >> 28) + 4u)) ^ s) * 277803737u;
     return (word >> 22) ^ word;
   }
-  float next_f32() { return (float)next_u32() / 4294967296.0f; }  // :132-134  f32(0xffffffffu) = 2^32
-  V direction() {                                                  // :135-144
+  float next_f32() { return (float)next_u32() / 4294967296.0f; }  // :130-132  f32(0xffffffffu) = 2^32
+  V direction() {                                                  // :133-142
     const float pi = 1.57079637f * 2.0f;                           // :1  acos(0.0) * 2.0
     const float z = next_f32() * 2.0f - 1.0f;
     const float theta = next_f32() * 2.0f * pi;
@@ -156,7 +156,7 @@ V calculate_normal(const WObject& o, V world) {
   const V v0 = mk(s[0], s[1], s[2]);
   return normalize(cross(mk(s[3], s[4], s[5]) - v0, mk(s[6], s[7], s[8]) - v0));
 }
-// bounding_box_code (sphere.rs:81-85, plane.rs:81-83, triangle.rs:189-193) + base_shader.wgsl:225-237
+// bounding_box_code (sphere.rs:81-85, plane.rs:81-83, triangle.rs:189-193) + base_shader.wgsl:212-224
 bool bounding_box_hit(const WObject& o, V pos, V dir) {
   const float* s = o.shape;
   V lo, hi;
@@ -176,7 +176,7 @@ bool bounding_box_hit(const WObject& o, V pos, V dir) {
   return tmax >= std::fmax(tmin, 0.0f);
 }
 
-// base_shader.wgsl:190-224
+// base_shader.wgsl:190-211
 bool closest_object(const Scene& sc, V pos, V dir, uint64_t* index, float* distance) {
   bool did = false;
   float best = -1.0f;
@@ -222,7 +222,7 @@ V trace_ray(const Scene& sc, Rng& g, V pos, V dir, uint64_t* rays, uint32_t* fir
   return color;
 }
 
-// :238-279: 1/det * adjugate, columns (A,D,G) (B,E,H) (C,F,I); m = columns (right, up, forward)
+// :228-267: 1/det * adjugate, columns (A,D,G) (B,E,H) (C,F,I); m = columns (right, up, forward)
 void inverse3x3(const V c0, const V c1, const V c2, V* o0, V* o1, V* o2) {
   const float a = c0.x, d = c0.y, g = c0.z, b = c1.x, e = c1.y, h = c1.z, c = c2.x, f = c2.y, i = c2.z;
   const float det = a * (e * i - f * h) - b * (d * i - f * g) + c * (d * h - e * g);
@@ -271,7 +271,7 @@ extern "C" {
 
 uint64_t wgsl_sizeof_object() { return sizeof(WObject); }
 
-// The RNG alone (base_shader.wgsl:97-134): the seed initRngSeed derives from a pixel's uv, then n draws of
+// The RNG alone (base_shader.wgsl:99-132): the seed initRngSeed derives from a pixel's uv, then n draws of
 // random_int() and — from a second copy of the stream — of random_float().
 void wgsl_rng_probe(float ux, float uy, uint32_t n, uint32_t* out_seed, uint32_t* out_u32, float* out_f32) {
   Rng a, b;

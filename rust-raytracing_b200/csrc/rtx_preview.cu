@@ -3,9 +3,9 @@
 // The reference has a second, real-time path: a WGSL fragment shader (raytracing/gpu/base_shader.wgsl, completed by
 // the per-shape snippets of object/sphere.rs:50-86, plane.rs:48-85, triangle.rs:138-194 through
 // gpu/gpu_state.rs:208-312) whose semantics differ from the CPU path's in every respect that matters to a pixel:
-// f32 throughout, a PCG-hash RNG seeded from the pixel's uv (:97-142), target jitter before origin jitter and
-// un-normalised random directions (:64-91, :135-144), max_bounces segments instead of max_bounces + 1 (:151-169), a
-// slab AABB pre-test per object (:190-237), Moeller-Trumbore triangles, the plane's RAW normal as its shading normal.
+// f32 throughout, a PCG-hash RNG seeded from the pixel's uv (:99-142), target jitter before origin jitter and
+// un-normalised random directions (:64-91, :133-142), max_bounces segments instead of max_bounces + 1 (:151-169), a
+// slab AABB pre-test per object (:190-224), Moeller-Trumbore triangles, the plane's RAW normal as its shading normal.
 // Executing that shader needs wgpu / Vulkan — unavailable on this box — but its arithmetic needs neither: this file
 // is that arithmetic, one thread per pixel, checked bit for bit against oracle/wgsl_oracle.cpp (whose header states
 // what is fixed where WGSL leaves a choice: IEEE f32 never fused, sin/cos = f64 libm rounded to f32, fminf/fmaxf).
@@ -118,7 +118,7 @@ __device__ __forceinline__ void sincos32(float x, const double* tab, float* s, f
   *c = __double2float_rn(dc);
 }
 
-// base_shader.wgsl:97-144
+// base_shader.wgsl:99-142
 struct PcgRng {
   uint32_t seed;
   __device__ __forceinline__ void init(float ux, float uy) {
@@ -126,7 +126,7 @@ struct PcgRng {
     const uint32_t ai = __float2uint_rz(pf_mul(ax, 4294967296.0f)), bi = __float2uint_rz(pf_mul(ay, 4294967296.0f));
     uint32_t h = ai ^ (bi * 0x85ebca6bu);
     h = (h ^ (h >> 16)) * 0x85ebca6bu;
-    uint32_t x = h ^ (h >> 13);  // jenkinsHash, :117-125
+    uint32_t x = h ^ (h >> 13);  // jenkinsHash, :115-123
     x += x << 10;
     x ^= x >> 6;
     x += x << 3;
@@ -156,18 +156,18 @@ struct PvScene {
   uint32_t n;
 };
 
-// base_shader.wgsl:190-237 with the per-shape distance snippets; returns the object index or MISS_ID
+// base_shader.wgsl:190-224 with the per-shape distance snippets; returns the object index or MISS_ID
 __device__ __forceinline__ uint32_t pv_closest(const PvScene& sc, F3 pos, F3 dir, float* out_d) {
   uint32_t best_i = MISS_ID;
   float best = -1.0f;
   // hoisted out of the object loop (the shader recomputes them per object, same operations on the same values)
-  const F3 inv = f3(pf_div(1.0f, dir.x), pf_div(1.0f, dir.y), pf_div(1.0f, dir.z));  // :229
+  const F3 inv = f3(pf_div(1.0f, dir.x), pf_div(1.0f, dir.y), pf_div(1.0f, dir.z));  // :216
   const F3 dn = pnormalize(dir);  // sphere.rs:63, plane.rs:68, triangle.rs:155
   const float a = pdot(dn, dn);   // sphere.rs:64
   for (uint32_t i = 0; i < sc.n; ++i) {
     const float4 lo = sc.f[PV_LO][i];
     const uint32_t type = __float_as_uint(lo.w);
-    if (type != 1u) {  // :225-237
+    if (type != 1u) {  // :212-224
       const float4 hi = sc.f[PV_HI][i];
       const F3 t0 = (xyz(lo) - pos) * inv, t1 = (xyz(hi) - pos) * inv;
       const float tmin = fmaxf(fmaxf(fminf(t0.x, t1.x), fminf(t0.y, t1.y)), fminf(t0.z, t1.z));
@@ -246,7 +246,7 @@ __global__ void __launch_bounds__(PV_BLOCK) preview_kernel(const __grid_constant
     const F3 fwd = pnormalize(f3(p.cam_dir[0], p.cam_dir[1], p.cam_dir[2]));
     const F3 right = pcross(fwd, f3(0.0f, 0.0f, 1.0f));
     const F3 up = pcross(fwd, right);
-    // inverse3x3 (:238-279) of the matrix whose COLUMNS are right, up, forward
+    // inverse3x3 (:228-267) of the matrix whose COLUMNS are right, up, forward
     const float ma = right.x, md = right.y, mg = right.z, mb = up.x, me = up.y, mh = up.z, mc = fwd.x, mf = fwd.y, mi = fwd.z;
     const float ei_fh = pf_sub(pf_mul(me, mi), pf_mul(mf, mh)), di_fg = pf_sub(pf_mul(md, mi), pf_mul(mf, mg)),
                 dh_eg = pf_sub(pf_mul(md, mh), pf_mul(me, mg));

@@ -33,7 +33,7 @@ np.savez_compressed(os.path.join(HERE, "wyrand_kat.npz"), seeds=seeds, u64=u, f6
 sc = scenes.sphere_demo(rays_per_pixel=2, max_bounces=5)
 r = oracle.render_preview_scene(sc, 96, 64)
 np.savez_compressed(os.path.join(HERE, "preview_sphere_demo_96x64_2spp.npz"), rgb=r["rgb"], ids=r["ids"], rays=np.uint64(r["rays"]))
-# and its RNG (base_shader.wgsl:97-134): seed + 6 draws for three uv values
+# and its RNG (base_shader.wgsl:99-132): seed + 6 draws for three uv values
 uv = np.array([[-0.25, 0.125], [0.0, 0.0], [0.4999, -0.4999]], dtype=np.float32)
 probe = [oracle.wgsl_rng_probe(float(a), float(b), 6) for a, b in uv]
 np.savez_compressed(os.path.join(HERE, "wgsl_pcg_kat.npz"), uv=uv, seed=np.array([p[0] for p in probe], dtype=np.uint32),

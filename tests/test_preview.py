@@ -3,7 +3,7 @@
 oracle/wgsl_oracle.cpp.  The gate is bit-exact f32 (the kernel is built -fmad=false, the oracle -ffp-contract=off;
 sin/cos are the f64 libm values rounded to f32 on both sides).  PARITY UNPINNED: the shader itself cannot be executed
 on this box (no wgpu), so the oracle is one reading of it with nothing reference-held behind it — the CPU tests below
-pin what can be pinned by hand: the RNG of base_shader.wgsl:97-134 and the loop bounds."""
+pin what can be pinned by hand: the RNG of base_shader.wgsl:99-132 and the loop bounds."""
 import numpy as np
 import pytest
 
@@ -28,7 +28,7 @@ def _mixed(rtx, spp=2, bounces=5):
 
 # ---- CPU: the oracle against hand-restated pieces of the shader ----------------------------------------------------
 def _pcg_seed(ux, uy):
-    """base_shader.wgsl:97-125 in numpy scalars."""
+    """base_shader.wgsl:99-123 in numpy scalars."""
     f = np.float32
     M = 0xFFFFFFFF
     ai = int(f(min(max(f(ux) + f(0.5), f(0.0)), f(0.999999))) * f(4294967296.0))
@@ -66,7 +66,7 @@ def test_oracle_loop_bounds_and_first_sample(rtx, oracle):
 
 
 def test_oracle_rng_matches_hand_restatement(rtx, oracle):
-    """uv -> initRngSeed -> random_int -> random_float (base_shader.wgsl:97-134) restated in numpy scalars, against the
+    """uv -> initRngSeed -> random_int -> random_float (base_shader.wgsl:99-132) restated in numpy scalars, against the
     oracle's generator, for the uv of every pixel of a small frame and a few edge values."""
     f = np.float32
     w, h = 7, 5
