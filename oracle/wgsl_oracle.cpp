@@ -13,7 +13,7 @@
 //    dot(a,b) = (a.x*b.x + a.y*b.y) + a.z*b.z;  length(v) = sqrt(dot(v,v));  normalize(v) = v / length(v);
 //    cross as written in the WGSL spec;  M * v = (col0*v.x + col1*v.y) + col2*v.z;
 //  * sin, cos: the f64 libm value rounded to f32;  min / max: fminf / fmaxf (the non-NaN operand wins);
-//  * literals: 1e-100 (sphere.rs:71) is not representable in f32 and becomes 0.0; EPSILON = f32(1e-8);
+//  * literals: 1e-100 (sphere.rs:69) is not representable in f32 and becomes 0.0; EPSILON = f32(1e-8);
 //    PI = acos(0.0) * 2.0 evaluated in f32 = 3.14159274;
 //  * the fragment's interpolated uv at the pixel centre: vs_main (:48-62) sets uv = clip position * (0.5, -0.5), so
 //    uv.x = (x + 0.5) / width - 0.5 and uv.y = -(clip y) / 2.  The image this file returns uses the row order of the
@@ -102,7 +102,7 @@ struct Dist {
   float d;
 };
 
-// object/sphere.rs:62-76
+// object/sphere.rs:52-75
 Dist sphere_distance(const float* s, V pos, V dir) {
   const V offset = pos - mk(s[0], s[1], s[2]);
   const V rd = normalize(dir);
@@ -113,7 +113,7 @@ Dist sphere_distance(const float* s, V pos, V dir) {
   if (disc < 0.0f) return Dist{false, 0.0f};  // `< 1e-100`: 0 in f32
   return Dist{true, (-b - std::sqrt(disc)) / (2.0f * a)};
 }
-// object/plane.rs:66-76
+// object/plane.rs:55-76
 Dist plane_distance(const float* s, V pos, V dir) {
   const V offset = pos - mk(s[0], s[1], s[2]);
   const V norm = normalize(mk(s[3], s[4], s[5]));
@@ -131,7 +131,7 @@ Dist triangle_distance(const float* s, V pos, V dir) {
   const V p = pos - v0;
   const V normal = cross(r, sv);
   if (dot(normalize(dir), normal) == 0.0f) return Dist{false, 0.0f};
-  // (:157-159 flips `normal`, which nothing reads afterwards)
+  // (:159-161 flips `normal`, which nothing reads afterwards)
   const V pvec = cross(dir, sv);
   const float det = dot(r, pvec);
   if (std::fabs(det) < EPSILON) return Dist{false, 0.0f};
@@ -148,7 +148,7 @@ Dist triangle_distance(const float* s, V pos, V dir) {
 Dist calculate_distance(const WObject& o, V pos, V dir) {
   return o.type == 0 ? sphere_distance(o.shape, pos, dir) : (o.type == 1 ? plane_distance(o.shape, pos, dir) : triangle_distance(o.shape, pos, dir));
 }
-// normal_calculation_code: sphere.rs:78-80, plane.rs:78-80 (NOT normalised), triangle.rs:142-148
+// normal_calculation_code: sphere.rs:76-78, plane.rs:77-79 (NOT normalised), triangle.rs:142-148
 V calculate_normal(const WObject& o, V world) {
   const float* s = o.shape;
   if (o.type == 0) return normalize(world - mk(s[0], s[1], s[2]));
@@ -156,7 +156,7 @@ V calculate_normal(const WObject& o, V world) {
   const V v0 = mk(s[0], s[1], s[2]);
   return normalize(cross(mk(s[3], s[4], s[5]) - v0, mk(s[6], s[7], s[8]) - v0));
 }
-// bounding_box_code (sphere.rs:81-85, plane.rs:81-83, triangle.rs:189-193) + base_shader.wgsl:212-224
+// bounding_box_code (sphere.rs:82-86, plane.rs:83-85, triangle.rs:190-194) + base_shader.wgsl:212-224
 bool bounding_box_hit(const WObject& o, V pos, V dir) {
   const float* s = o.shape;
   V lo, hi;

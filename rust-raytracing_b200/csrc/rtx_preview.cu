@@ -33,7 +33,7 @@ enum : int { PV_A = 0, PV_B, PV_C, PV_D, PV_E, PV_LO, PV_HI, PV_MAT0, PV_MAT1, P
 // PV_C   -                              (normalize(normal), -)       (s = v2 - v0, -)
 // PV_D   -                              -                            (cross(r, s), -)
 // PV_E   -                              -                            (normalize(cross(r, s)), -)
-// PV_LO  (box min, type as bits)   PV_HI (box max, -)       — planes have no box (bounding_box_code, plane.rs:81-83)
+// PV_LO  (box min, type as bits)   PV_HI (box max, -)       — planes have no box (bounding_box_code, plane.rs:83-85)
 // PV_MAT0 (max(base_color, 0), roughness)   PV_MAT1 (emission_color, -)
 constexpr uint32_t PV_SMEM_BYTES = 96u * 1024u;
 constexpr int PV_BLOCK = 128;  // 16 x 8 pixels
@@ -162,8 +162,8 @@ __device__ __forceinline__ uint32_t pv_closest(const PvScene& sc, F3 pos, F3 dir
   float best = -1.0f;
   // hoisted out of the object loop (the shader recomputes them per object, same operations on the same values)
   const F3 inv = f3(pf_div(1.0f, dir.x), pf_div(1.0f, dir.y), pf_div(1.0f, dir.z));  // :216
-  const F3 dn = pnormalize(dir);  // sphere.rs:63, plane.rs:68, triangle.rs:155
-  const float a = pdot(dn, dn);   // sphere.rs:64
+  const F3 dn = pnormalize(dir);  // sphere.rs:64, plane.rs:68, triangle.rs:156
+  const float a = pdot(dn, dn);   // sphere.rs:65
   for (uint32_t i = 0; i < sc.n; ++i) {
     const float4 lo = sc.f[PV_LO][i];
     const uint32_t type = __float_as_uint(lo.w);
@@ -176,14 +176,14 @@ __device__ __forceinline__ uint32_t pv_closest(const PvScene& sc, F3 pos, F3 dir
     }
     const float4 A = sc.f[PV_A][i];
     float d;
-    if (type == 0u) {  // sphere.rs:62-76
+    if (type == 0u) {  // sphere.rs:52-75
       const F3 offset = pos - xyz(A);
       const float b = pf_mul(2.0f, pdot(offset, dn));
       const float c = pf_sub(pdot(offset, offset), pf_mul(A.w, A.w));
       const float disc = pf_sub(pf_mul(b, b), pf_mul(pf_mul(4.0f, a), c));
       if (disc < 0.0f) continue;
       d = pf_div(pf_sub(-b, pf_sqrt(disc)), pf_mul(2.0f, a));
-    } else if (type == 1u) {  // plane.rs:66-76
+    } else if (type == 1u) {  // plane.rs:55-76
       const F3 offset = pos - xyz(A);
       const F3 norm = xyz(sc.f[PV_C][i]);
       if (pdot(dn, norm) >= 0.0f || pdot(offset, norm) <= 0.0f) continue;
@@ -295,7 +295,7 @@ __global__ void __launch_bounds__(PV_BLOCK) preview_kernel(const __grid_constant
           if (light.x == 0.0f && light.y == 0.0f && light.z == 0.0f) {
             end = true;
           } else {
-            // calculate_normal: sphere.rs:78-80, plane.rs:78-80 (the RAW normal), triangle.rs:142-148
+            // calculate_normal: sphere.rs:76-78, plane.rs:77-79 (the RAW normal), triangle.rs:142-148
             const uint32_t type = __float_as_uint(sc.f[PV_LO][hit].w);
             F3 n;
             if (type == 0u) n = pnormalize(pos - xyz(sc.f[PV_A][hit]));
@@ -353,7 +353,7 @@ static void build_preview_soa(const rtx_scene* s, std::vector<float>& out, uint3
       const double* r = &s->sph[(size_t)k * SPH_STRIDE];
       const float cx = (float)r[0], cy = (float)r[1], cz = (float)r[2], rad = (float)s->sph_radius[k];
       put(PV_A, i, cx, cy, cz, rad);
-      put(PV_LO, i, cx - rad, cy - rad, cz - rad, bits(0u));  // sphere.rs:81-85
+      put(PV_LO, i, cx - rad, cy - rad, cz - rad, bits(0u));  // sphere.rs:82-86
       put(PV_HI, i, cx + rad, cy + rad, cz + rad, 0.0f);
     } else if (kind == REF_PLANE) {
       const double* r = &s->pl[(size_t)k * PL_STRIDE];
@@ -374,7 +374,7 @@ static void build_preview_soa(const rtx_scene* s, std::vector<float>& out, uint3
       put(PV_D, i, nrm.x, nrm.y, nrm.z, 0.0f);
       put(PV_E, i, nh.x, nh.y, nh.z, 0.0f);
       put(PV_LO, i, std::fmin(std::fmin(v0.x, v1.x), v2.x), std::fmin(std::fmin(v0.y, v1.y), v2.y),
-          std::fmin(std::fmin(v0.z, v1.z), v2.z), bits(2u));  // triangle.rs:189-193
+          std::fmin(std::fmin(v0.z, v1.z), v2.z), bits(2u));  // triangle.rs:190-194
       put(PV_HI, i, std::fmax(std::fmax(v0.x, v1.x), v2.x), std::fmax(std::fmax(v0.y, v1.y), v2.y),
           std::fmax(std::fmax(v0.z, v1.z), v2.z), 0.0f);
     }
