@@ -318,7 +318,7 @@ rtx_status rtx_peer_close(int32_t device, void* d_ptr);
 rtx_status rtx_scene_render_to_rgb8(rtx_scene* scene, uint32_t width, uint32_t height, uint64_t seed, uint32_t flags,
                                     uint8_t* out_rgb8, rtx_stats* out_stats);
 /* ---- the f32 "preview" mode: the arithmetic of the reference's wgpu backend ----------------------------------
- * ≙ gpu::Scene::render (raytracing/gpu/scene.rs:26-52) → GpuState::render (gpu/gpu_state.rs:78-107) → the fragment
+ * ≙ gpu::Scene::render (raytracing/gpu/scene.rs:27-29) → GpuState::render (gpu/gpu_state.rs:78-107) → the fragment
  * shader raytracing/gpu/base_shader.wgsl:64-267 with the shape snippets of object/sphere.rs:50-86, plane.rs:48-85,
  * triangle.rs:138-194.  Same scene handle, other semantics: f32 throughout, PCG-hash RNG seeded from the pixel (no
  * `seed`), max_bounces segments (not + 1), AABB pre-test, Moeller-Trumbore triangles, raw plane normals.  The scene,

@@ -163,7 +163,7 @@ class Scene {
     check(rtx_scene_render_to_rgb8(h_, (uint32_t)width, (uint32_t)height, seed, RTX_ACCEL_AUTO, out.data(), nullptr), h_);
     return out;
   }
-  // ≙ gpu::Scene::render (raytracing/gpu/scene.rs:26-52): the wgpu backend's f32 image (base_shader.wgsl), row 0 = bottom
+  // ≙ gpu::Scene::render (raytracing/gpu/scene.rs:27-29): the wgpu backend's f32 image (base_shader.wgsl), row 0 = bottom
   std::vector<float> render_preview(size_t width, size_t height) {
     sync();
     std::vector<float> out(width * height * 3);
