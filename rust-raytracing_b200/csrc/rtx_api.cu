@@ -1036,7 +1036,7 @@ rtx_status rtx_scene_render(rtx_scene* s, uint32_t width, uint32_t height, uint6
   const size_t npix = (size_t)width * height;
   // A caller buffer in pinned, device-mapped host memory (rtx_host_alloc, cudaHostAlloc, cudaHostRegister) is
   // written by the render kernel itself: every finished pixel is a posted store over PCIe while the rest of the
-  // frame is still rendering, so there is no device frame and no copy after the kernel (RTX_ZERO_COPY=0 turns it
+  // frame is still rendering, so there is no device frame and no copy after the kernel (a measurement build can turn it
   // off).  Pageable buffers go through the scene's device frame + cudaMemcpyAsync.
   double* k_rgb = want_rgb ? mapped_device_pointer(out_rgb) : nullptr;
   uint32_t* k_ids = out_primary_hit_id ? mapped_device_pointer(out_primary_hit_id) : nullptr;
